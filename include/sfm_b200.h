@@ -1,0 +1,102 @@
+/*
+ * sfm_b200.h -- C ABI of libsfm_b200.so, the B200 (sm_100a) numerical core for the
+ * Phase-1 SfM hot path of pvrohin/Structure-from-Motion-.
+ *
+ * Conventions:
+ *   - every entry point is extern "C", returns int (0 = SFM_OK, else an SFM_E_* code,
+ *     never throws), takes plain pointers and sizes only;
+ *   - pointers named d_* are DEVICE pointers owned by the caller; the library never
+ *     allocates device memory behind the caller's back: each entry point that needs
+ *     scratch has a *_workspace_bytes() query and takes the workspace explicitly;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it and the
+ *     call returns without synchronising unless stated otherwise;
+ *   - all real data is float64, all indices int32, row-major.
+ *
+ * Each entry point cites the reference interface it replaces ("Phase 1/<file>:<line>").
+ * The reference-side binding (ctypes) is shown in INTEGRATION.md.
+ */
+#ifndef SFM_B200_H
+#define SFM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SFM_OK 0
+#define SFM_E_INVALID 1      /* bad argument (null pointer, negative size, ...) */
+#define SFM_E_CUDA 2         /* a CUDA runtime call or launch failed; see sfm_last_cuda_error() */
+#define SFM_E_WORKSPACE 3    /* workspace too small */
+#define SFM_E_NCCL 4         /* NCCL missing or a collective failed */
+#define SFM_E_NOT_CONVERGED 5
+
+/* ABI version of this header; bumped on any signature change. */
+int sfm_abi_version(void);
+/* cudaGetErrorString of the last failing CUDA call seen by the library (static storage). */
+const char *sfm_last_cuda_error(void);
+/* Number of kernel launches issued by the library since load (all entry points). Used by
+ * bench.py for the "gpu_launches" claim. */
+int64_t sfm_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Host-side sampler: the reference draws one `random.sample(range(n), k)` per RANSAC
+ * hypothesis from CPython's global Mersenne Twister (GetInliersRANSAC.py:55, PnPRANSAC.py:49).
+ * This advances a copy of that MT19937 state exactly as CPython's random.sample would for
+ * `count` consecutive calls and writes the index sets. HOST pointers.
+ *   mt_state : 624 words, mt_index : position (both from random.getstate(), written back)
+ *   out      : [count, k] int32
+ * ------------------------------------------------------------------------------------------ */
+int sfm_mt_sample_stream(uint32_t *mt_state, int32_t *mt_index, int32_t n, int32_t k,
+                         int64_t count, int32_t *out);
+
+/* ------------------------------------------------------------------------------------------
+ * F-matrix RANSAC (replaces GetInliersRANSAC.py:53-92 + EstimateFundamentalMatrix.py:30-78)
+ * d_x1x2   : [n,4] rows (x1,y1,x2,y2)
+ * d_sample : [h,8] int32 indices into 0..n-1 (host-generated reference stream)
+ * ------------------------------------------------------------------------------------------ */
+
+/* K1: Hartley-normalised 8-point estimate for h samples -> d_F [h,9] (row-major 3x3 each,
+ * normalised by F[2][2] like EstimateFundamentalMatrix.py:78). */
+int sfm_f8pt_batch(const double *d_x1x2, int32_t n, const int32_t *d_sample, int32_t h,
+                   double *d_F, void *stream);
+
+/* K2: inlier count of every hypothesis over all n correspondences with the reference's
+ * symmetric epipolar distance (GetInliersRANSAC.py:67-82). d_counts [h] int32 (overwritten). */
+int sfm_f_score_count(const double *d_x1x2, int32_t n, const double *d_F, int32_t h,
+                      double threshold, int32_t *d_counts, void *stream);
+
+/* K3: first-maximum argmax (strict '>' rule of GetInliersRANSAC.py:85).
+ * d_best[0] = index of the first hypothesis with the maximum count (global index =
+ * local index + idx_offset), d_best[1] = that count. d_key (uint64, optional, may be null)
+ * receives (count << 32) | (0xFFFFFFFF - global_idx) for a cross-GPU max-reduce. */
+int sfm_argmax_first(const int32_t *d_counts, int32_t h, int32_t idx_offset, int32_t *d_best,
+                     uint64_t *d_key, void *stream);
+
+/* K4: inlier mask + per-point error for ONE fundamental matrix d_Fone[9]
+ * (GetInliersRANSAC.py:67-81). d_mask [n] uint8, d_err [n] float64 (may be null). */
+int sfm_f_inlier_mask(const double *d_x1x2, int32_t n, const double *d_Fone, double threshold,
+                      uint8_t *d_mask, double *d_err, void *stream);
+
+/* K1..K4 chained on one stream. Outputs:
+ *   d_F      [h,9]  all hypotheses        d_counts [h]
+ *   d_best   [2]    (winner index, count) d_Fbest  [9]   (copy of d_F[winner])
+ *   d_mask   [n]    inlier mask of the winner (all zero when the best count is 0)
+ *   d_err    [n]    winner's per-point error in the reference's exact formula (may be null) */
+int sfm_f_ransac(const double *d_x1x2, int32_t n, const int32_t *d_sample, int32_t h,
+                 double threshold, double *d_F, int32_t *d_counts, int32_t *d_best,
+                 double *d_Fbest, uint8_t *d_mask, double *d_err, void *stream);
+
+/* EstimateFundamentalMatrix for ANY n >= 8 (EstimateFundamentalMatrix.py:3-83 called with all
+ * points). d_ws: workspace of sfm_fundamental_npt_workspace_bytes(n) bytes. d_F [9]. */
+size_t sfm_fundamental_npt_workspace_bytes(int32_t n);
+int sfm_fundamental_npt(const double *d_x1, const double *d_x2, int32_t n, double *d_F,
+                        void *d_ws, size_t ws_bytes, void *stream);
+
+/* @@MORE@@ (further sections are appended above this marker as the path widens) */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SFM_B200_H */

@@ -1,0 +1,84 @@
+"""ctypes binding of libsfm_b200.so (the C ABI declared in include/sfm_b200.h).
+
+There is deliberately no fallback: if the shared library is missing and cannot be built,
+or an entry point fails, the caller gets an exception.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+from . import build as _build
+
+_lock = threading.Lock()
+_lib = None
+
+c_f64p = C.c_void_p   # device or host pointers are passed as integers
+c_i32p = C.c_void_p
+c_u8p = C.c_void_p
+c_vp = C.c_void_p
+
+# name -> (restype, [argtypes]); must list EVERY symbol include/sfm_b200.h declares
+# (tests/test_abi.py parses the header and checks both directions).
+SIGNATURES = {
+    "sfm_abi_version": (C.c_int, []),
+    "sfm_last_cuda_error": (C.c_char_p, []),
+    "sfm_launch_count": (C.c_int64, []),
+    "sfm_mt_sample_stream": (C.c_int, [c_vp, c_vp, C.c_int32, C.c_int32, C.c_int64, c_vp]),
+    "sfm_f8pt_batch": (C.c_int, [c_f64p, C.c_int32, c_i32p, C.c_int32, c_f64p, c_vp]),
+    "sfm_f_score_count": (C.c_int, [c_f64p, C.c_int32, c_f64p, C.c_int32, C.c_double, c_i32p, c_vp]),
+    "sfm_argmax_first": (C.c_int, [c_i32p, C.c_int32, C.c_int32, c_i32p, c_vp, c_vp]),
+    "sfm_f_inlier_mask": (C.c_int, [c_f64p, C.c_int32, c_f64p, C.c_double, c_u8p, c_f64p, c_vp]),
+    "sfm_f_ransac": (C.c_int, [c_f64p, C.c_int32, c_i32p, C.c_int32, C.c_double, c_f64p, c_i32p,
+                               c_i32p, c_f64p, c_u8p, c_f64p, c_vp]),
+    "sfm_fundamental_npt_workspace_bytes": (C.c_size_t, [C.c_int32]),
+    "sfm_fundamental_npt": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_vp, C.c_size_t, c_vp]),
+}
+
+_ERR = {1: "SFM_E_INVALID", 2: "SFM_E_CUDA", 3: "SFM_E_WORKSPACE", 4: "SFM_E_NCCL",
+        5: "SFM_E_NOT_CONVERGED"}
+
+
+class SfmError(RuntimeError):
+    pass
+
+
+def lib_path() -> str:
+    return _build.LIB_PATH
+
+
+def load(build_if_missing: bool = True):
+    """Load (building first when stale and nvcc is available) and type the library."""
+    global _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        path = _build.LIB_PATH
+        if build_if_missing and _build.is_stale():
+            try:
+                _build.build()
+            except Exception as e:  # no nvcc on the box: use the shipped .so if there is one
+                if not os.path.exists(path):
+                    raise SfmError(
+                        f"libsfm_b200.so is missing and could not be built ({e}); "
+                        "there is no CPU fallback") from e
+        if not os.path.exists(path):
+            raise SfmError(f"{path} not found; run __graft_entry__.build() (no CPU fallback)")
+        lib = C.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+        return lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = load().sfm_last_cuda_error().decode(errors="replace") if rc == 2 else ""
+        raise SfmError(f"{what} failed: {_ERR.get(rc, rc)} {msg}")
+
+
+def launch_count() -> int:
+    return int(load().sfm_launch_count())

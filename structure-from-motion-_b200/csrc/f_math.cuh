@@ -1,0 +1,223 @@
+// f_math.cuh -- per-thread arithmetic of the fundamental-matrix path.
+//
+// Replaces (reference, "Phase 1/"):
+//   EstimateFundamentalMatrix.py:30-78  -> f8pt_from_sample()
+//   GetInliersRANSAC.py:67-81           -> f_is_inlier() / f_error_exact()
+//
+// Quirks kept on purpose: design rows encode n1^T F n2 while the
+// de-normalisation is T2^T F T1 (Q1); +1e-8 on the Hartley scale and on both line norms
+// (Q2); inlier test is strict '<' and NaN is never an inlier (Q3, Q10); the metric is the
+// mean of the two point-to-epipolar-line distances, not Sampson (Q12).
+#pragma once
+#include "sfm_common.cuh"
+
+namespace sfm {
+
+// ---- one-sided (Hestenes) Jacobi on a 3x3 ------------------------------------------------
+// Rotates columns p,q of G (3x3, column access through the three row arrays) and of V so
+// that the two columns of G become orthogonal. Returns true when a rotation was applied.
+SFM_HD bool jacobi_pair3(double &g0p, double &g1p, double &g2p, double &g0q, double &g1q,
+                         double &g2q, double &v0p, double &v1p, double &v2p, double &v0q,
+                         double &v1q, double &v2q) {
+    double app = g0p * g0p + g1p * g1p + g2p * g2p;
+    double aqq = g0q * g0q + g1q * g1q + g2q * g2q;
+    double apq = g0p * g0q + g1p * g1q + g2p * g2q;
+    // converged for this pair (also covers zero columns)
+    if (fabs(apq) <= 1e-15 * sqrt(app * aqq) || apq == 0.0) return false;
+    double zeta = (aqq - app) / (2.0 * apq);
+    double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+    double c = 1.0 / sqrt(1.0 + t * t);
+    double s = c * t;
+    double a, b;
+    a = g0p; b = g0q; g0p = c * a - s * b; g0q = s * a + c * b;
+    a = g1p; b = g1q; g1p = c * a - s * b; g1q = s * a + c * b;
+    a = g2p; b = g2q; g2p = c * a - s * b; g2q = s * a + c * b;
+    a = v0p; b = v0q; v0p = c * a - s * b; v0q = s * a + c * b;
+    a = v1p; b = v1q; v1p = c * a - s * b; v1q = s * a + c * b;
+    a = v2p; b = v2q; v2p = c * a - s * b; v2q = s * a + c * b;
+    return true;
+}
+
+// Rank-2 projection of a 3x3 M (row-major m[9]) : U diag(s0,s1,0) V^T, i.e. what
+// EstimateFundamentalMatrix.py:70-72 does with numpy's SVD. In place.
+SFM_HD void rank2_project3(double *m) {
+    double g00 = m[0], g01 = m[1], g02 = m[2];
+    double g10 = m[3], g11 = m[4], g12 = m[5];
+    double g20 = m[6], g21 = m[7], g22 = m[8];
+    double v00 = 1, v01 = 0, v02 = 0, v10 = 0, v11 = 1, v12 = 0, v20 = 0, v21 = 0, v22 = 1;
+    for (int sweep = 0; sweep < 40; ++sweep) {
+        bool r0 = jacobi_pair3(g00, g10, g20, g01, g11, g21, v00, v10, v20, v01, v11, v21);
+        bool r1 = jacobi_pair3(g00, g10, g20, g02, g12, g22, v00, v10, v20, v02, v12, v22);
+        bool r2 = jacobi_pair3(g01, g11, g21, g02, g12, g22, v01, v11, v21, v02, v12, v22);
+        if (!(r0 | r1 | r2)) break;
+    }
+    // G = M V has orthogonal columns sigma_j u_j. Drop the smallest one:
+    // M2 = sum over the two largest columns of g_j v_j^T.
+    double n0 = g00 * g00 + g10 * g10 + g20 * g20;
+    double n1 = g01 * g01 + g11 * g11 + g21 * g21;
+    double n2 = g02 * g02 + g12 * g12 + g22 * g22;
+    double w0 = 1.0, w1 = 1.0, w2 = 1.0;
+    if (n0 <= n1 && n0 <= n2) w0 = 0.0;
+    else if (n1 <= n0 && n1 <= n2) w1 = 0.0;
+    else w2 = 0.0;
+    g00 *= w0; g10 *= w0; g20 *= w0;
+    g01 *= w1; g11 *= w1; g21 *= w1;
+    g02 *= w2; g12 *= w2; g22 *= w2;
+    m[0] = g00 * v00 + g01 * v01 + g02 * v02;
+    m[1] = g00 * v10 + g01 * v11 + g02 * v12;
+    m[2] = g00 * v20 + g01 * v21 + g02 * v22;
+    m[3] = g10 * v00 + g11 * v01 + g12 * v02;
+    m[4] = g10 * v10 + g11 * v11 + g12 * v12;
+    m[5] = g10 * v20 + g11 * v21 + g12 * v22;
+    m[6] = g20 * v00 + g21 * v01 + g22 * v02;
+    m[7] = g20 * v10 + g21 * v11 + g22 * v12;
+    m[8] = g20 * v20 + g21 * v21 + g22 * v22;
+}
+
+// ---- null vector of an 8x9 matrix ----------------------------------------------------------
+// a[r][c] = row r (r = 0..7) of the design matrix. The reference takes Vt[-1] of the full
+// SVD (EstimateFundamentalMatrix.py:65-67), which for an 8x9 matrix is the unit vector
+// orthogonal to all eight rows. We get the same vector (up to the sign that the F[2][2]
+// normalisation removes) as the last column of Q in the Householder QR of A^T (9x8): it is
+// backward stable like the SVD, needs ~1.3 kflop instead of a full Jacobi SVD and every
+// index below is a compile-time constant after unrolling, so A lives in registers.
+// Rank-deficient samples (duplicated matches) have a >1-dimensional null space;
+// LAPACK's pick there is rounding noise, ours is "orthogonal to the rows, from e9".
+SFM_HD void null_vector_8x9(double (&a)[8][9], double (&q)[9]) {
+    double beta[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        // column j of B = A^T is row j of A; entries j..8 are active
+        double nrm2 = 0.0;
+#pragma unroll
+        for (int i = j; i < 9; ++i) nrm2 += a[j][i] * a[j][i];
+        double nrm = sqrt(nrm2);
+        double x0 = a[j][j];
+        double alpha = (x0 >= 0.0) ? -nrm : nrm;
+        double v0 = x0 - alpha;
+        // v = (v0, a[j][j+1..8]);  v^T v = nrm2 - x0^2 + v0^2 = 2 nrm (nrm + |x0|)
+        double vtv = 2.0 * nrm * (nrm + fabs(x0));
+        double b = (vtv > 0.0) ? 2.0 / vtv : 0.0;
+        beta[j] = b;
+        a[j][j] = v0;
+#pragma unroll
+        for (int k = j + 1; k < 8; ++k) {
+            double dot = 0.0;
+#pragma unroll
+            for (int i = j; i < 9; ++i) dot += a[j][i] * a[k][i];
+            dot *= b;
+#pragma unroll
+            for (int i = j; i < 9; ++i) a[k][i] -= dot * a[j][i];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) q[i] = 0.0;
+    q[8] = 1.0;
+#pragma unroll
+    for (int j = 7; j >= 0; --j) {
+        double dot = 0.0;
+#pragma unroll
+        for (int i = j; i < 9; ++i) dot += a[j][i] * q[i];
+        dot *= beta[j];
+#pragma unroll
+        for (int i = j; i < 9; ++i) q[i] -= dot * a[j][i];
+    }
+}
+
+// ---- Hartley-normalised 8-point ------------------------------------------------------------
+// px1[i],py1[i],px2[i],py2[i]: the eight sampled correspondences. F: row-major 3x3,
+// divided by F[2][2] (EstimateFundamentalMatrix.py:78; a zero F[2][2] yields inf/nan exactly
+// as numpy does, and such a hypothesis then scores zero inliers).
+SFM_HD void f8pt_from_sample(const double (&px1)[8], const double (&py1)[8],
+                             const double (&px2)[8], const double (&py2)[8], double *F) {
+    double mx1 = 0, my1 = 0, mx2 = 0, my2 = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { mx1 += px1[i]; my1 += py1[i]; mx2 += px2[i]; my2 += py2[i]; }
+    mx1 *= 0.125; my1 *= 0.125; mx2 *= 0.125; my2 *= 0.125;
+    double d1 = 0, d2 = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        double ax = px1[i] - mx1, ay = py1[i] - my1;
+        double bx = px2[i] - mx2, by = py2[i] - my2;
+        d1 += sqrt(ax * ax + ay * ay);
+        d2 += sqrt(bx * bx + by * by);
+    }
+    const double SQRT2 = 1.4142135623730951;
+    double s1 = SQRT2 / (d1 * 0.125 + 1e-8);
+    double s2 = SQRT2 / (d2 * 0.125 + 1e-8);
+    double tx1 = -s1 * mx1, ty1 = -s1 * my1, tx2 = -s2 * mx2, ty2 = -s2 * my2;
+
+    double a[8][9];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        // normalized = T @ [x, y, 1]  (EstimateFundamentalMatrix.py:54-55)
+        double x1 = s1 * px1[i] + tx1, y1 = s1 * py1[i] + ty1;
+        double x2 = s2 * px2[i] + tx2, y2 = s2 * py2[i] + ty2;
+        a[i][0] = x1 * x2; a[i][1] = x1 * y2; a[i][2] = x1;
+        a[i][3] = y1 * x2; a[i][4] = y1 * y2; a[i][5] = y1;
+        a[i][6] = x2;      a[i][7] = y2;      a[i][8] = 1.0;
+    }
+    double f[9];
+    null_vector_8x9(a, f);
+    rank2_project3(f);
+    // F = T2^T Fh T1   with T = [[s,0,tx],[0,s,ty],[0,0,1]]
+    // (Fh T1): column ops; then T2^T: row ops.
+    double g[9];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        g[3 * r + 0] = f[3 * r + 0] * s1;
+        g[3 * r + 1] = f[3 * r + 1] * s1;
+        g[3 * r + 2] = f[3 * r + 0] * tx1 + f[3 * r + 1] * ty1 + f[3 * r + 2];
+    }
+    double o[9];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        o[0 + c] = s2 * g[0 + c];
+        o[3 + c] = s2 * g[3 + c];
+        o[6 + c] = tx2 * g[0 + c] + ty2 * g[3 + c] + g[6 + c];
+    }
+    double inv = o[8];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) F[i] = o[i] / inv;
+}
+
+// ---- inlier test -----------------------------------------------------------------------------
+// err = (|e|/(n1+1e-8) + |e|/(n2+1e-8))/2 < thr   (GetInliersRANSAC.py:72-81), evaluated in
+// the algebraically identical division-free form
+//     |e| (n1+n2+2eps) < 2 thr (n1+eps)(n2+eps)
+// (both denominators are positive, so the inequality direction is preserved). two_thr = 2*thr.
+// NaN anywhere makes the comparison false, like numpy's.
+struct FMat {
+    double f0, f1, f2, f3, f4, f5, f6, f7, f8;
+};
+
+SFM_HD bool f_is_inlier(const FMat &F, double x1, double y1, double x2, double y2,
+                        double two_thr) {
+    double a = fma(F.f0, x1, fma(F.f1, y1, F.f2));
+    double b = fma(F.f3, x1, fma(F.f4, y1, F.f5));
+    double c = fma(F.f6, x1, fma(F.f7, y1, F.f8));
+    double e = fma(x2, a, fma(y2, b, c));
+    double p = fma(F.f0, x2, fma(F.f3, y2, F.f6));
+    double q = fma(F.f1, x2, fma(F.f4, y2, F.f7));
+    double n1 = fast_sqrt_pos(fma(a, a, fma(b, b, SFM_TINY)));
+    double n2 = fast_sqrt_pos(fma(p, p, fma(q, q, SFM_TINY)));
+    double u = n1 + n2;
+    double lhs = fabs(e) * (u + 2e-8);
+    double rhs = two_thr * fma(n1, n2, fma(1e-8, u, 1e-16));
+    return lhs < rhs;
+}
+
+// The reference's expression verbatim (for the reported per-point error of the winner).
+SFM_HD double f_error_exact(const FMat &F, double x1, double y1, double x2, double y2) {
+    double a = F.f0 * x1 + F.f1 * y1 + F.f2;
+    double b = F.f3 * x1 + F.f4 * y1 + F.f5;
+    double c = F.f6 * x1 + F.f7 * y1 + F.f8;
+    double e = x2 * a + y2 * b + c;
+    double p = F.f0 * x2 + F.f3 * y2 + F.f6;
+    double q = F.f1 * x2 + F.f4 * y2 + F.f7;
+    double dist1 = fabs(e) / (sqrt(a * a + b * b) + 1e-8);
+    double dist2 = fabs(e) / (sqrt(p * p + q * q) + 1e-8);
+    return (dist1 + dist2) / 2;
+}
+
+}  // namespace sfm

@@ -1,0 +1,214 @@
+// f_ransac.cu -- K1..K4 of the F-matrix RANSAC path for sm_100a.
+//
+//   K1 f8pt_kernel        EstimateFundamentalMatrix.py:30-78 for every sampled 8-tuple
+//   K2 f_score_kernel     GetInliersRANSAC.py:67-82: inlier count of every hypothesis
+//   K3 argmax_first_kernel GetInliersRANSAC.py:85: first hypothesis with the maximum count
+//   K4 f_mask_kernel      GetInliersRANSAC.py:81,87 for the winner
+//
+// Layout: correspondences [n,4] f64 rows (x1,y1,x2,y2) = two 16-byte vector loads per row;
+// samples [h,8] i32; hypotheses [h,9] f64; counts [h] i32.
+//
+// K2 is the hot kernel: h x n point-hypothesis tests. One thread owns one hypothesis (its F
+// stays in 18 registers), a block stages a chunk of correspondences in shared memory with
+// 16-byte loads and every warp reads them back as broadcasts, so the inner loop is pure FP64
+// pipe work (~37 FP64 instructions per test, no divisions, one MUFU per square root). The grid
+// is (hypothesis tiles) x (point chunks); partial counts are merged with integer atomics, so
+// the result is order-independent and bit-reproducible.
+#include "f_math.cuh"
+
+namespace sfm {
+
+// ------------------------------------------------------------------------------------ K1
+__global__ void __launch_bounds__(128)
+f8pt_kernel(const double *__restrict__ x1x2, const int32_t *__restrict__ sample, int h,
+            double *__restrict__ Fout) {
+    int hyp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (hyp >= h) return;
+    double px1[8], py1[8], px2[8], py2[8];
+    const int4 *sp = reinterpret_cast<const int4 *>(sample + (size_t)hyp * 8);
+    int4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
+    int idx[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const double2 *row = reinterpret_cast<const double2 *>(x1x2 + (size_t)idx[i] * 4);
+        double2 a = __ldg(row), b = __ldg(row + 1);
+        px1[i] = a.x; py1[i] = a.y; px2[i] = b.x; py2[i] = b.y;
+    }
+    double F[9];
+    f8pt_from_sample(px1, py1, px2, py2, F);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) Fout[(size_t)hyp * 9 + i] = F[i];
+}
+
+// ------------------------------------------------------------------------------------ K2
+constexpr int K2_THREADS = 256;
+
+__global__ void __launch_bounds__(K2_THREADS)
+f_score_kernel(const double *__restrict__ x1x2, int n, const double *__restrict__ Fall, int h,
+               double two_thr, int chunk, int32_t *__restrict__ counts) {
+    extern __shared__ double2 spts[];  // chunk rows, two double2 per row
+    const int p0 = blockIdx.y * chunk;
+    const int np = min(chunk, n - p0);
+    {
+        const double2 *src = reinterpret_cast<const double2 *>(x1x2) + (size_t)p0 * 2;
+        for (int i = threadIdx.x; i < np * 2; i += K2_THREADS) spts[i] = __ldg(src + i);
+    }
+    const int hyp = blockIdx.x * K2_THREADS + threadIdx.x;
+    FMat F;
+    {
+        // out-of-range threads score hypothesis h-1 again and drop the result: keeps the
+        // warp convergent around __syncthreads and the loop branch-free.
+        const double *f = Fall + (size_t)min(hyp, h - 1) * 9;
+        F.f0 = __ldg(f + 0); F.f1 = __ldg(f + 1); F.f2 = __ldg(f + 2);
+        F.f3 = __ldg(f + 3); F.f4 = __ldg(f + 4); F.f5 = __ldg(f + 5);
+        F.f6 = __ldg(f + 6); F.f7 = __ldg(f + 7); F.f8 = __ldg(f + 8);
+    }
+    __syncthreads();
+    int cnt = 0;
+#pragma unroll 4
+    for (int i = 0; i < np; ++i) {
+        double2 a = spts[2 * i], b = spts[2 * i + 1];
+        cnt += f_is_inlier(F, a.x, a.y, b.x, b.y, two_thr) ? 1 : 0;
+    }
+    if (hyp < h && cnt) atomicAdd(&counts[hyp], cnt);
+}
+
+// ------------------------------------------------------------------------------------ K3
+// key = (count << 32) | (0xFFFFFFFF - global index): max(key) = largest count, and among equal
+// counts the LOWEST index, which is the reference's strict '>' update rule.
+__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long w = __shfl_xor_sync(0xffffffffu, v, o);
+        v = w > v ? w : v;
+    }
+    return v;
+}
+
+__global__ void __launch_bounds__(1024)
+argmax_first_kernel(const int32_t *__restrict__ counts, int h, int idx_offset,
+                    int32_t *__restrict__ best, unsigned long long *__restrict__ key_out) {
+    __shared__ unsigned long long swarp[32];
+    unsigned long long k = 0ull;  // count 0 at "index 0xFFFFFFFF": loses to any real entry
+    for (int i = threadIdx.x; i < h; i += blockDim.x) {
+        unsigned long long c = (unsigned long long)(unsigned int)max(counts[i], 0);
+        unsigned long long cand = (c << 32) | (unsigned long long)(0xFFFFFFFFu - (unsigned int)(i + idx_offset));
+        k = cand > k ? cand : k;
+    }
+    k = warp_max_u64(k);
+    if ((threadIdx.x & 31) == 0) swarp[threadIdx.x >> 5] = k;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        k = threadIdx.x < (blockDim.x >> 5) ? swarp[threadIdx.x] : 0ull;
+        k = warp_max_u64(k);
+        if (threadIdx.x == 0) {
+            best[0] = (int32_t)(0xFFFFFFFFu - (unsigned int)(k & 0xFFFFFFFFull));
+            best[1] = (int32_t)(k >> 32);
+            if (key_out) *key_out = k;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------ K4
+// F is read through a device pointer + optional device index so the winner never has to make
+// a round trip to the host: Fone = Fbase + 9 * (best ? best[0] - idx_offset : 0).
+__global__ void __launch_bounds__(256)
+f_mask_kernel(const double *__restrict__ x1x2, int n, const double *__restrict__ Fbase,
+              const int32_t *__restrict__ best, int idx_offset, int h, double two_thr,
+              uint8_t *__restrict__ mask, double *__restrict__ err, double *__restrict__ Fcopy) {
+    int sel = 0;
+    bool valid = true;
+    if (best) {
+        sel = best[0] - idx_offset;
+        valid = best[1] > 0 && sel >= 0 && sel < h;
+        if (!valid) sel = 0;
+    }
+    const double *f = Fbase + (size_t)sel * 9;
+    FMat F = {f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7], f[8]};
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (Fcopy && i < 9) Fcopy[i] = f[i];
+    if (i >= n) return;
+    const double2 *row = reinterpret_cast<const double2 *>(x1x2) + (size_t)i * 2;
+    double2 a = __ldg(row), b = __ldg(row + 1);
+    mask[i] = (valid && f_is_inlier(F, a.x, a.y, b.x, b.y, two_thr)) ? 1 : 0;
+    if (err) err[i] = f_error_exact(F, a.x, a.y, b.x, b.y);
+}
+
+// chunk of correspondences per block: large enough to amortise the F load and the atomics,
+// small enough that (tiles x chunks) covers the 148 SMs a few times over.
+static int pick_chunk(int n, int h) {
+    int tiles = ceil_div(h, K2_THREADS);
+    int chunk = 1024;  // 32 KB of shared memory
+    while (chunk > 128 && (long long)tiles * ceil_div(n, chunk) < 4LL * sm_count()) chunk >>= 1;
+    return chunk;
+}
+
+}  // namespace sfm
+
+using namespace sfm;
+
+extern "C" int sfm_f8pt_batch(const double *d_x1x2, int32_t n, const int32_t *d_sample,
+                              int32_t h, double *d_F, void *stream) {
+    if (!d_x1x2 || !d_sample || !d_F || n < 8 || h < 0) return SFM_E_INVALID;
+    if (h == 0) return SFM_OK;
+    f8pt_kernel<<<ceil_div(h, 128), 128, 0, as_stream(stream)>>>(d_x1x2, d_sample, h, d_F);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+extern "C" int sfm_f_score_count(const double *d_x1x2, int32_t n, const double *d_F, int32_t h,
+                                 double threshold, int32_t *d_counts, void *stream) {
+    if (!d_x1x2 || !d_F || !d_counts || n < 0 || h < 0) return SFM_E_INVALID;
+    if (h == 0) return SFM_OK;
+    cudaStream_t st = as_stream(stream);
+    SFM_CUDA_TRY(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)h, st));
+    if (n == 0) return SFM_OK;
+    int chunk = pick_chunk(n, h);
+    size_t smem = (size_t)chunk * 32;
+    static bool attr_set = false;
+    if (!attr_set) {
+        SFM_CUDA_TRY(cudaFuncSetAttribute(f_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          1024 * 32));
+        attr_set = true;
+    }
+    dim3 grid(ceil_div(h, K2_THREADS), ceil_div(n, chunk));
+    f_score_kernel<<<grid, K2_THREADS, smem, st>>>(d_x1x2, n, d_F, h, 2.0 * threshold, chunk,
+                                                   d_counts);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+extern "C" int sfm_argmax_first(const int32_t *d_counts, int32_t h, int32_t idx_offset,
+                                int32_t *d_best, uint64_t *d_key, void *stream) {
+    if (!d_counts || !d_best || h < 0) return SFM_E_INVALID;
+    argmax_first_kernel<<<1, 1024, 0, as_stream(stream)>>>(
+        d_counts, h, idx_offset, d_best, reinterpret_cast<unsigned long long *>(d_key));
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+extern "C" int sfm_f_inlier_mask(const double *d_x1x2, int32_t n, const double *d_Fone,
+                                 double threshold, uint8_t *d_mask, double *d_err, void *stream) {
+    if (!d_x1x2 || !d_Fone || !d_mask || n < 0) return SFM_E_INVALID;
+    if (n == 0) return SFM_OK;
+    f_mask_kernel<<<ceil_div(n, 256), 256, 0, as_stream(stream)>>>(
+        d_x1x2, n, d_Fone, nullptr, 0, 1, 2.0 * threshold, d_mask, d_err, nullptr);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+extern "C" int sfm_f_ransac(const double *d_x1x2, int32_t n, const int32_t *d_sample, int32_t h,
+                            double threshold, double *d_F, int32_t *d_counts, int32_t *d_best,
+                            double *d_Fbest, uint8_t *d_mask, double *d_err, void *stream) {
+    if (!d_x1x2 || !d_sample || !d_F || !d_counts || !d_best || !d_Fbest || !d_mask || n < 8 ||
+        h < 1)
+        return SFM_E_INVALID;
+    int rc;
+    if ((rc = sfm_f8pt_batch(d_x1x2, n, d_sample, h, d_F, stream)) != SFM_OK) return rc;
+    if ((rc = sfm_f_score_count(d_x1x2, n, d_F, h, threshold, d_counts, stream)) != SFM_OK) return rc;
+    if ((rc = sfm_argmax_first(d_counts, h, 0, d_best, nullptr, stream)) != SFM_OK) return rc;
+    f_mask_kernel<<<ceil_div(max(n, 9), 256), 256, 0, as_stream(stream)>>>(
+        d_x1x2, n, d_F, d_best, 0, h, 2.0 * threshold, d_mask, d_err, d_Fbest);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
