@@ -1,0 +1,281 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark: RANSAC F-hypotheses/s on BASELINE.json configs[1]
+(synthetic two-view F-RANSAC: 50k correspondences, 30% outliers, 100k hypotheses per GPU).
+
+    python bench.py --gpus N --steps K --warmup W            (our arm; torchrun for N > 1)
+    python bench.py --impl reference --gpus N --steps K ...  (reference arm: CPU oracle port)
+
+One step = one full RANSAC over the per-GPU batch: K1 8-point hypotheses, K2 consensus
+scoring, K3 first-max argmax, K4 winner mask (+ one 8-byte NCCL max-allreduce for N > 1).
+Prints ONE JSON line (rank 0). See DESIGN.md "Measurement" for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import random
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_PTS = 50_000
+N_HYP = 100_000          # per GPU (weak scaling: the hypothesis stream grows with N)
+THRESH = 0.06            # the reference default (GetInliersRANSAC.py:5, Wrapper_dev.py:105)
+DATA_SEED = 20260102
+RNG_SEED = 12345
+METRIC = "RANSAC F-hypotheses/sec"
+UNIT = "hypotheses/s"
+WORKLOAD = "C2 two-view F-RANSAC: 50k correspondences, 30% outliers, 100k hypotheses/GPU"
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "measured (MEASURED_PEAKS.json)"
+    return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.samples, self.stop_evt, self.index = [], threading.Event(), index
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([c.strip() for c in out.splitlines()[0].split(",")])
+            except Exception:
+                pass
+            self.stop_evt.wait(0.2)
+
+    def __enter__(self):
+        self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop_evt.set()
+        self.thread.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[3 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": float(self.samples[0][1]) if self.samples[0][1].replace(".", "").isdigit() else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def make_inputs(n_hyp_total):
+    from sfm_b200 import sampler, scenes
+    sc = scenes.two_view(n=N_PTS, seed=DATA_SEED)
+    random.seed(RNG_SEED)
+    samples = sampler.sample_stream(N_PTS, 8, n_hyp_total)
+    return sc, samples
+
+
+# ------------------------------------------------------------------------------------------
+# CPU side: the oracle port of GetInliersRANSAC.py:53-92 (per-hypothesis numpy, like the reference)
+# ------------------------------------------------------------------------------------------
+def _cpu_chunk(args):
+    x1, x2, samples, thr = args
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
+    from oracle import sfm_oracle as so
+    t = time.perf_counter()
+    d = so.f_ransac_detailed(x1, x2, thr, samples)
+    return time.perf_counter() - t, int(d["best_count"])
+
+
+def cpu_baseline_single(sc, samples, n_hyp=4000):
+    """Rank 0, N=1 only: the oracle port on ONE core (the reference is single-threaded)."""
+    dt, _ = _cpu_chunk((sc["x1"], sc["x2"], samples[:n_hyp], THRESH))
+    return {"value": n_hyp / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"first {n_hyp} hypotheses of the same stream over all {N_PTS} correspondences "
+                      f"({dt:.1f} s)"}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU algorithm (oracle port; the Python reference cannot
+    travel to the GPU box) on all host cores, one process per core over hypothesis chunks."""
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    cores = os.cpu_count() or 1
+    per_core = 48                                   # ~0.1 s per core per step at 1.9 ms/hypothesis
+    h_step = per_core * cores
+    sc, samples = make_inputs(h_step * (args.steps + args.warmup))
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores) as pool:
+        def step(i):
+            blk = samples[i * h_step:(i + 1) * h_step]
+            jobs = [(sc["x1"], sc["x2"], blk[c * per_core:(c + 1) * per_core], THRESH) for c in range(cores)]
+            t = time.perf_counter()
+            pool.map(_cpu_chunk, jobs)
+            return time.perf_counter() - t
+        for i in range(args.warmup):
+            step(i)
+        dts = [step(args.warmup + i) for i in range(args.steps)]
+    total = sum(dts)
+    value = h_step * args.steps / total
+    sample = (f"each step = {h_step} hypotheses of the same stream ({per_core}/core) over all "
+              f"{N_PTS} correspondences")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": {"workload": WORKLOAD, "threshold": THRESH, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def run_ours(args, rank, world):
+    import torch
+    import torch.distributed as dist
+    from sfm_b200 import _lib, device, ransac
+
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = _lib.load()
+    sc, samples_all = make_inputs(N_HYP * world)
+    x1x2 = np.ascontiguousarray(np.hstack([sc["x1"], sc["x2"]]))
+    d_x = device.to_device(x1x2)
+    d_s_all = device.to_device(samples_all, np.int32)
+    d_s = d_s_all[rank * N_HYP:(rank + 1) * N_HYP]
+    plan = ransac.FRansacPlan(N_PTS, N_HYP)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
+
+    def step():
+        if world > 1:
+            return plan.run_sharded(d_x, d_s_all, THRESH, rank, world)
+        return plan.run(d_x, d_s, THRESH)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        step()
+    barrier()
+    launches0 = _lib.launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    with ClockSampler(local) as clocks:
+        barrier()
+        for a, b in ev:
+            flush.zero_()                      # L2 flush between timed iterations (outside the events)
+            a.record()
+            r = step()
+            b.record()
+        barrier()
+    launches = _lib.launch_count() - launches0
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    value = N_HYP * world * args.steps / (ms_total * 1e-3)
+
+    # dominant kernel (K2 consensus scoring) timed alone on the launching stream
+    k2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    st = device.stream()
+    for a, b in k2:
+        flush.zero_()
+        a.record()
+        _lib.check(lib.sfm_f_score_count(device.ptr(d_x), N_PTS, device.ptr(plan.r.F), N_HYP, THRESH,
+                                         device.ptr(plan.r.counts), st), "sfm_f_score_count")
+        b.record()
+    torch.cuda.synchronize()
+    k2_ms = sum(a.elapsed_time(b) for a, b in k2) / args.steps
+    peaks, peak_src = measured_peaks()
+    alg_bytes = (32.0 * N_PTS + 76.0) * N_HYP
+    achieved = alg_bytes / (k2_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "f_score_kernel (K2)", "achieved": achieved,
+                "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
+                "traffic": None, "peak_source": peak_src, "kernel_ms": k2_ms,
+                "algorithmic_bytes_per_launch": alg_bytes,
+                "note": "algorithmic bytes = (32 B x N + 76 B) per hypothesis (SURVEY 8d); the 1.6 MB "
+                        "correspondence set is SMEM/L2 resident, so the physical limiter is the FP64 pipe: "
+                        "see fp64_pipe",
+                "fp64_pipe": {"fp64_instr_per_test": 31, "tests_per_launch": float(N_PTS) * N_HYP,
+                              "achieved_tinstr_s": 31.0 * N_PTS * N_HYP / (k2_ms * 1e-3) / 1e12}}
+
+    # end to end through the drop-in signature: host numpy in, host numpy out, RNG replay, H2D, D2H
+    index = np.arange(N_PTS)
+    e2e_steps = max(1, min(args.steps, 5))
+    random.seed(RNG_SEED)
+    ransac.GetInliersRANSAC(sc["x1"], sc["x2"], index, THRESH, N_HYP)       # warm
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        inl, outl, F = ransac.GetInliersRANSAC(sc["x1"], sc["x2"], index, THRESH, N_HYP)
+    torch.cuda.synchronize()
+    te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e = {"value": N_HYP * world * e2e_steps / float(te.item()), "unit": UNIT,
+           "h2d_bytes_per_step": int(x1x2.nbytes + N_HYP * 8 * 4), "d2h_bytes_per_step": 80 + N_PTS,
+           "api": "sfm_b200.ransac.GetInliersRANSAC(points1, points2, index, 0.06, 100000) per GPU "
+                  "(host numpy in/out; includes the MT19937 sample replay)",
+           "steps": e2e_steps}
+
+    best = r.best.cpu().numpy()
+    if rank == 0:
+        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+               "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
+               "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+               "data": "synthetic",
+               "config": {"workload": WORKLOAD, "threshold": THRESH, "n_correspondences": N_PTS,
+                          "hypotheses_per_gpu": N_HYP, "l2": "256 MiB flush write between timed steps",
+                          "winner": [int(best[0]), int(best[1])]},
+               "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches),
+               "clocks": clocks.summary()}
+        if world == 1:
+            out["cpu_baseline"] = cpu_baseline_single(sc, samples_all, n_hyp=args.cpu_hyp)
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-hyp", type=int, default=6000, help="hypotheses in the 1-core CPU baseline sample")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        if world != args.gpus and world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N > 1")
+        run_ours(args, rank, world)
+
+
+if __name__ == "__main__":
+    main()

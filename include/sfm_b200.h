@@ -88,6 +88,15 @@ int sfm_f_ransac(const double *d_x1x2, int32_t n, const int32_t *d_sample, int32
                  double threshold, double *d_F, int32_t *d_counts, int32_t *d_best,
                  double *d_Fbest, uint8_t *d_mask, double *d_err, void *stream);
 
+/* Multi-GPU tail of the hypothesis-sharded RANSAC: d_key holds the max-allreduced
+ * (count << 32) | (0xFFFFFFFF - global_idx). Decodes the global winner into d_best[2],
+ * recomputes its F from d_sample_all [h_total,8] (the whole stream, replicated on every rank)
+ * into d_Fbest[9] and writes the winner's mask / error like sfm_f_ransac. */
+int sfm_f_winner_from_key(const double *d_x1x2, int32_t n, const int32_t *d_sample_all,
+                          int32_t h_total, const uint64_t *d_key, double threshold,
+                          int32_t *d_best, double *d_Fbest, uint8_t *d_mask, double *d_err,
+                          void *stream);
+
 /* EstimateFundamentalMatrix for ANY n >= 8 (EstimateFundamentalMatrix.py:3-83 called with all
  * points). d_ws: workspace of sfm_fundamental_npt_workspace_bytes(n) bytes. d_F [9]. */
 size_t sfm_fundamental_npt_workspace_bytes(int32_t n);

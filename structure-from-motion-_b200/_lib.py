@@ -32,6 +32,8 @@ SIGNATURES = {
     "sfm_f_inlier_mask": (C.c_int, [c_f64p, C.c_int32, c_f64p, C.c_double, c_u8p, c_f64p, c_vp]),
     "sfm_f_ransac": (C.c_int, [c_f64p, C.c_int32, c_i32p, C.c_int32, C.c_double, c_f64p, c_i32p,
                                c_i32p, c_f64p, c_u8p, c_f64p, c_vp]),
+    "sfm_f_winner_from_key": (C.c_int, [c_f64p, C.c_int32, c_i32p, C.c_int32, c_vp, C.c_double, c_i32p,
+                                        c_f64p, c_u8p, c_f64p, c_vp]),
     "sfm_fundamental_npt_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "sfm_fundamental_npt": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_vp, C.c_size_t, c_vp]),
 }

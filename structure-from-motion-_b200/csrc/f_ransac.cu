@@ -119,7 +119,8 @@ f_mask_kernel(const double *__restrict__ x1x2, int n, const double *__restrict__
     int sel = 0;
     bool valid = true;
     if (best) {
-        sel = best[0] - idx_offset;
+        // idx_offset < 0: Fbase already IS the winner's F (multi-GPU tail); only validity is read
+        sel = idx_offset < 0 ? 0 : best[0] - idx_offset;
         valid = best[1] > 0 && sel >= 0 && sel < h;
         if (!valid) sel = 0;
     }
@@ -209,6 +210,53 @@ extern "C" int sfm_f_ransac(const double *d_x1x2, int32_t n, const int32_t *d_sa
     if ((rc = sfm_argmax_first(d_counts, h, 0, d_best, nullptr, stream)) != SFM_OK) return rc;
     f_mask_kernel<<<ceil_div(max(n, 9), 256), 256, 0, as_stream(stream)>>>(
         d_x1x2, n, d_F, d_best, 0, h, 2.0 * threshold, d_mask, d_err, d_Fbest);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+// ---- multi-GPU tail ---------------------------------------------------------------------------
+// After the 8-byte max-allreduce of the packed key every rank decodes the global winner and
+// recomputes its F from the winning sample (all ranks hold the whole sample stream), so no
+// broadcast of F or of the mask is needed and all ranks end with identical bits.
+namespace sfm {
+__global__ void f_winner_from_key_kernel(const double *__restrict__ x1x2,
+                                         const int32_t *__restrict__ sample_all, int h_total,
+                                         const unsigned long long *__restrict__ key,
+                                         int32_t *__restrict__ best, double *__restrict__ Fbest) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long k = *key;
+    int idx = (int)(0xFFFFFFFFu - (unsigned int)(k & 0xFFFFFFFFull));
+    int cnt = (int)(k >> 32);
+    best[0] = idx;
+    best[1] = cnt;
+    if (cnt <= 0 || idx < 0 || idx >= h_total) {
+        best[1] = 0;
+        for (int i = 0; i < 9; ++i) Fbest[i] = 0.0;
+        return;
+    }
+    double px1[8], py1[8], px2[8], py2[8];
+    for (int i = 0; i < 8; ++i) {
+        const double *row = x1x2 + (size_t)sample_all[(size_t)idx * 8 + i] * 4;
+        px1[i] = row[0]; py1[i] = row[1]; px2[i] = row[2]; py2[i] = row[3];
+    }
+    f8pt_from_sample(px1, py1, px2, py2, Fbest);
+}
+}  // namespace sfm
+
+extern "C" int sfm_f_winner_from_key(const double *d_x1x2, int32_t n, const int32_t *d_sample_all,
+                                     int32_t h_total, const uint64_t *d_key, double threshold,
+                                     int32_t *d_best, double *d_Fbest, uint8_t *d_mask,
+                                     double *d_err, void *stream) {
+    if (!d_x1x2 || !d_sample_all || !d_key || !d_best || !d_Fbest || !d_mask || n < 8 || h_total < 1)
+        return SFM_E_INVALID;
+    f_winner_from_key_kernel<<<1, 32, 0, as_stream(stream)>>>(
+        d_x1x2, d_sample_all, h_total, reinterpret_cast<const unsigned long long *>(d_key), d_best,
+        d_Fbest);
+    SFM_LAUNCH_CHECK();
+    // Fbase = d_Fbest, selected entry 0 (idx_offset = best[0]); valid iff best[1] > 0
+    f_mask_kernel<<<ceil_div(n, 256), 256, 0, as_stream(stream)>>>(
+        d_x1x2, n, d_Fbest, d_best, /*idx_offset (device-side)*/ -1, 1, 2.0 * threshold, d_mask, d_err,
+        nullptr);
     SFM_LAUNCH_CHECK();
     return SFM_OK;
 }

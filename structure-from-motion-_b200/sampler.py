@@ -1,0 +1,42 @@
+"""RANSAC sample streams drawn from CPython's GLOBAL `random` generator, exactly as the
+reference consumes it: one random.sample(range(n), min(k, n)) per hypothesis
+(GetInliersRANSAC.py:55, PnPRANSAC.py:49). The fast path replays the Mersenne Twister in C
+(csrc/mt_sample.cpp) and writes the advanced state back, so code that interleaves on the same
+stream (the wrapper's homography RANSAC, GetHomographyInliers.py:126) sees identical draws."""
+from __future__ import annotations
+
+import ctypes as C
+import random
+
+import numpy as np
+
+from . import _lib
+
+
+def _python_stream(n: int, k: int, count: int) -> np.ndarray:
+    out = np.empty((count, k), dtype=np.int32)
+    for i in range(count):
+        out[i] = random.sample(range(n), k)
+    return out
+
+
+def sample_stream(n: int, k: int, count: int) -> np.ndarray:
+    """[count, min(k,n)] int32 index sets; advances the global `random` state like the reference."""
+    k = min(k, n)
+    if count <= 0 or k <= 0:
+        return np.empty((max(count, 0), max(k, 0)), dtype=np.int32)
+    inst = getattr(random, "_inst", None)
+    fast = (type(inst) is random.Random and getattr(random.sample, "__self__", None) is inst
+            and n < 2 ** 31 and k <= 64 and count >= 16)
+    if fast:
+        st = random.getstate()
+        fast = st[0] == 3 and len(st[1]) == 625
+    if not fast:
+        return _python_stream(n, k, count)
+    mt = np.array(st[1][:624], dtype=np.uint32)
+    idx = C.c_int32(st[1][624])
+    out = np.empty((count, k), dtype=np.int32)
+    rc = _lib.load().sfm_mt_sample_stream(mt.ctypes.data, C.addressof(idx), n, k, count, out.ctypes.data)
+    _lib.check(rc, "sfm_mt_sample_stream")
+    random.setstate((3, tuple(int(v) for v in mt) + (int(idx.value),), st[2]))
+    return out
