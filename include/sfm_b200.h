@@ -103,6 +103,37 @@ size_t sfm_fundamental_npt_workspace_bytes(int32_t n);
 int sfm_fundamental_npt(const double *d_x1, const double *d_x2, int32_t n, double *d_F,
                         void *d_ws, size_t ws_bytes, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * LM status word written by the batched solvers: (status << 16) | trial_steps, status =
+ * 1 gtol, 2 ftol, 3 xtol, 5 iteration cap, -1 failed (non-finite residuals; the input is
+ * returned unchanged, like the reference's except branches). Tolerance `tol` applies to the
+ * MINPACK ftol/xtol/gtol definitions (scipy default 1e-8; pass <= 1e-12 to converge at least
+ * as tightly as the reference).
+ * ------------------------------------------------------------------------------------------ */
+
+/* K5: NonLinearTriangulation (NonLinearTriangulation.py:53-130) for n points and ONE camera
+ * pair. h_P1,h_P2: HOST 3x4 projection matrices K[R|-RC] (row-major, 12 doubles each).
+ * d_x1,d_x2 [n,2]; d_X0 [n,3] initial points; d_X [n,3] out (may alias d_X0);
+ * d_cost [n] final 0.5|r|^2 (may be null); d_status [n] (may be null). */
+int sfm_nltri(const double *h_P1, const double *h_P2, const double *d_x1, const double *d_x2,
+              const double *d_X0, int32_t n, int32_t max_iter, double tol, double *d_X,
+              double *d_cost, int32_t *d_status, void *stream);
+
+/* K6: PnP-RANSAC consensus scoring (PnPRANSAC.py:59-69). d_P [h,12] hypothesis projection
+ * matrices K[R|-RC]; d_X [n,3]; d_x [n,2]; d_counts [h] (overwritten). Pair with
+ * sfm_argmax_first for the strict-'>' first-maximum rule (PnPRANSAC.py:72). */
+int sfm_pnp_score_count(const double *d_P, const double *d_X, const double *d_x, int32_t n,
+                        int32_t h, double threshold, int32_t *d_counts, void *stream);
+
+/* K7: NonLinearPnP (NonlinearPnP.py:47-123) for a batch of independent registrations.
+ * h_K: HOST 3x3 intrinsics. Problem b uses rows d_offsets[b]..d_offsets[b+1]-1 of d_X [M,3] /
+ * d_x [M,2]. d_rt0/d_rt [B,6] = [rotvec, t = -R C] in/out; d_cost [B], d_status [B] may be null.
+ * A problem with fewer than 4 points returns its input (NonlinearPnP.py:82-84). */
+int sfm_nlpnp_batch(const double *h_K, const double *d_X, const double *d_x,
+                    const int32_t *d_offsets, int32_t n_problems, const double *d_rt0,
+                    int32_t max_iter, double tol, double *d_rt, double *d_cost,
+                    int32_t *d_status, void *stream);
+
 /* @@MORE@@ (further sections are appended above this marker as the path widens) */
 
 #ifdef __cplusplus

@@ -34,6 +34,12 @@ SIGNATURES = {
                                c_i32p, c_f64p, c_u8p, c_f64p, c_vp]),
     "sfm_f_winner_from_key": (C.c_int, [c_f64p, C.c_int32, c_i32p, C.c_int32, c_vp, C.c_double, c_i32p,
                                         c_f64p, c_u8p, c_f64p, c_vp]),
+    "sfm_nltri": (C.c_int, [c_vp, c_vp, c_f64p, c_f64p, c_f64p, C.c_int32, C.c_int32, C.c_double,
+                            c_f64p, c_f64p, c_i32p, c_vp]),
+    "sfm_pnp_score_count": (C.c_int, [c_f64p, c_f64p, c_f64p, C.c_int32, C.c_int32, C.c_double,
+                                      c_i32p, c_vp]),
+    "sfm_nlpnp_batch": (C.c_int, [c_vp, c_f64p, c_f64p, c_i32p, C.c_int32, c_f64p, C.c_int32,
+                                  C.c_double, c_f64p, c_f64p, c_i32p, c_vp]),
     "sfm_fundamental_npt_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "sfm_fundamental_npt": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_vp, C.c_size_t, c_vp]),
 }
