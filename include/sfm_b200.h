@@ -134,6 +134,61 @@ int sfm_nlpnp_batch(const double *h_K, const double *d_X, const double *d_x,
                     int32_t max_iter, double tol, double *d_rt, double *d_cost,
                     int32_t *d_status, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Bundle adjustment (replaces perform_bundle_adjustment's least_squares call,
+ * BundleAdjustment.py:205-212, and bundle_adjustment_residuals, BundleAdjustment.py:43-110).
+ * Sparse form of the reference's problem:
+ *   d_cam     [n_cams,6]  [rotvec(3), t(3) = -R C]       (BundleAdjustment.py:183-192)
+ *   d_pts     [n_pts,3]                                   (BundleAdjustment.py:195-197)
+ *   d_obs     [n_obs,2]   observed pixel of observation o
+ *   d_cam_idx [n_obs], d_pt_idx [n_obs]  int32; observations sorted by point, i.e. d_pt_idx
+ *             non-decreasing (the reference's own order, BundleAdjustment.py:164-169)
+ *   h_K       HOST 3x3 intrinsics (row-major)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct sfm_ba_options {
+    int32_t max_trials;  /* scipy max_nfev: residual evaluations at trial points (reference: 100) */
+    int32_t verbose;     /* 1: one line per trial step on stderr */
+    double ftol, xtol, gtol; /* MINPACK / scipy stopping tolerances (reference: scipy default 1e-8) */
+    double lambda0;      /* initial damping of (J^T J + lambda D^2); D = Jacobian column norms */
+} sfm_ba_options;
+
+typedef struct sfm_ba_result {
+    double cost0, cost;  /* 0.5 |r|^2 before / after (scipy result.cost, BundleAdjustment.py:236) */
+    double gnorm;        /* MINPACK gtol measure at the last linearisation */
+    double lambda;       /* final damping */
+    int32_t status;      /* scipy codes: -1 non-finite residuals (inputs returned unchanged),
+                            0 max_trials reached, 1 gtol, 2 ftol, 3 xtol, 4 ftol and xtol */
+    int32_t n_linearisations; /* LM iterations: Jacobian / normal-equation builds */
+    int32_t n_trials;    /* trial steps solved and evaluated (>= n_linearisations - 1) */
+    int32_t n_chol_fail; /* trial steps rejected because S was not numerically positive definite */
+} sfm_ba_result;
+
+void sfm_ba_default_options(sfm_ba_options *opts);
+size_t sfm_ba_workspace_bytes(int32_t n_cams, int32_t n_pts, int32_t n_obs);
+
+/* K8 alone: residual vector of bundle_adjustment_residuals (BundleAdjustment.py:43-110),
+ * d_r [n_obs,2] interleaved [du,dv] = observed - projected (may be null), d_cost[0] = 0.5 |r|^2
+ * (may be null). Synchronises the stream once (index validation). */
+int sfm_ba_residuals(const double *d_cam, const double *d_pts, const double *d_obs,
+                     const int32_t *d_cam_idx, const int32_t *d_pt_idx, int32_t n_cams,
+                     int32_t n_pts, int32_t n_obs, const double *h_K, double *d_r, double *d_cost,
+                     void *d_ws, size_t ws_bytes, void *stream);
+
+/* The whole LM solve (K8-K12). d_cam / d_pts are updated in place; h_result is a HOST struct.
+ * Synchronous: returns after the last step (the LM controller reads a few scalars per trial).
+ * SFM_E_INVALID when an index is out of range or d_pt_idx is not sorted. */
+int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, const int32_t *d_cam_idx,
+                 const int32_t *d_pt_idx, int32_t n_cams, int32_t n_pts, int32_t n_obs,
+                 const double *h_K, const sfm_ba_options *opts, sfm_ba_result *h_result,
+                 void *d_ws, size_t ws_bytes, void *stream);
+
+/* K11 alone: dense SPD solve S x = g by the blocked Cholesky used inside sfm_ba_solve.
+ * d_S [n,n] row-major (lower triangle read), d_g [n], d_x [n] out, d_fail[0] = 1 when a pivot
+ * was not positive. */
+size_t sfm_chol_solve_workspace_bytes(int32_t n);
+int sfm_chol_solve(const double *d_S, const double *d_g, int32_t n, double *d_x, int32_t *d_fail,
+                   void *d_ws, size_t ws_bytes, void *stream);
+
 /* @@MORE@@ (further sections are appended above this marker as the path widens) */
 
 #ifdef __cplusplus

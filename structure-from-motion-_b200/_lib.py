@@ -42,7 +42,28 @@ SIGNATURES = {
                                   C.c_double, c_f64p, c_f64p, c_i32p, c_vp]),
     "sfm_fundamental_npt_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "sfm_fundamental_npt": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_vp, C.c_size_t, c_vp]),
+    "sfm_ba_default_options": (None, [c_vp]),
+    "sfm_ba_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
+    "sfm_ba_residuals": (C.c_int, [c_f64p, c_f64p, c_f64p, c_i32p, c_i32p, C.c_int32, C.c_int32, C.c_int32,
+                                   c_vp, c_f64p, c_f64p, c_vp, C.c_size_t, c_vp]),
+    "sfm_ba_solve": (C.c_int, [c_f64p, c_f64p, c_f64p, c_i32p, c_i32p, C.c_int32, C.c_int32, C.c_int32,
+                               c_vp, c_vp, c_vp, c_vp, C.c_size_t, c_vp]),
+    "sfm_chol_solve_workspace_bytes": (C.c_size_t, [C.c_int32]),
+    "sfm_chol_solve": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_i32p, c_vp, C.c_size_t, c_vp]),
 }
+
+
+class BAOptions(C.Structure):
+    """sfm_ba_options (include/sfm_b200.h)."""
+    _fields_ = [("max_trials", C.c_int32), ("verbose", C.c_int32), ("ftol", C.c_double),
+                ("xtol", C.c_double), ("gtol", C.c_double), ("lambda0", C.c_double)]
+
+
+class BAResult(C.Structure):
+    """sfm_ba_result (include/sfm_b200.h)."""
+    _fields_ = [("cost0", C.c_double), ("cost", C.c_double), ("gnorm", C.c_double), ("lambda_", C.c_double),
+                ("status", C.c_int32), ("n_linearisations", C.c_int32), ("n_trials", C.c_int32),
+                ("n_chol_fail", C.c_int32)]
 
 _ERR = {1: "SFM_E_INVALID", 2: "SFM_E_CUDA", 3: "SFM_E_WORKSPACE", 4: "SFM_E_NCCL",
         5: "SFM_E_NOT_CONVERGED"}

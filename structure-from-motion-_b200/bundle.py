@@ -1,0 +1,190 @@
+"""Host side of bundle adjustment: mirrors BundleAdjustment.py (project_points :8-40,
+bundle_adjustment_residuals :43-110, perform_bundle_adjustment :113-242; names, argument order,
+return order, prints and the 'return the inputs' failure convention) and drives K8-K12 through
+the C ABI (sfm_ba_solve / sfm_ba_residuals). The sparse entry points (`ba_solve_sparse`,
+`BAProblem`) sit next to the reference signature for the C3/C5-scale workloads, where the
+reference's dense (n_features x n_images) arrays do not scale."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+from scipy.spatial.transform import Rotation
+
+from . import _lib, device
+
+BA_MAX_NFEV = 100          # BundleAdjustment.py:211
+REF_TOL = 1e-8             # scipy least_squares defaults (ftol = xtol = gtol)
+
+STATUS_TEXT = {-1: "non-finite residuals", 0: "max evaluations", 1: "gtol", 2: "ftol", 3: "xtol",
+               4: "ftol and xtol"}
+
+
+def _hptr(a: np.ndarray) -> int:
+    return a.ctypes.data
+
+
+# ---------------------------------------------------------------------------------------------
+# sparse device-level API
+# ---------------------------------------------------------------------------------------------
+class BAProblem:
+    """Device-resident sparse BA problem: observations sorted by point (the reference's order,
+    BundleAdjustment.py:164-169). Holds the workspace, so repeated solves do not allocate."""
+
+    def __init__(self, n_cams: int, n_pts: int, cam_idx, pt_idx, obs, K):
+        cam_idx = np.ascontiguousarray(cam_idx, np.int32)
+        pt_idx = np.ascontiguousarray(pt_idx, np.int32)
+        obs = np.ascontiguousarray(obs, np.float64).reshape(-1, 2)
+        if not (len(cam_idx) == len(pt_idx) == len(obs)):
+            raise ValueError("cam_idx, pt_idx and obs must have one entry per observation")
+        if len(pt_idx) > 1 and np.any(np.diff(pt_idx) < 0):
+            order = np.argsort(pt_idx, kind="stable")       # point-major, original order within a point
+            cam_idx, pt_idx, obs = cam_idx[order], pt_idx[order], obs[order]
+        self.n_cams, self.n_pts, self.n_obs = int(n_cams), int(n_pts), int(len(obs))
+        self.K = np.ascontiguousarray(K, np.float64).reshape(3, 3)
+        self.d_cam_idx = device.to_device(cam_idx, np.int32)
+        self.d_pt_idx = device.to_device(pt_idx, np.int32)
+        self.d_obs = device.to_device(obs)
+        lib = _lib.load()
+        self.ws_bytes = int(lib.sfm_ba_workspace_bytes(self.n_cams, self.n_pts, self.n_obs))
+        if self.ws_bytes == 0:
+            raise ValueError("empty bundle adjustment problem")
+        self.ws = device.empty((self.ws_bytes,), torch.uint8)
+
+    def residuals_device(self, d_cam, d_pts, want_r=True):
+        """K8: (d_r [n_obs,2] or None, d_cost [1]) at the given parameters."""
+        d_r = device.empty((self.n_obs, 2), torch.float64) if want_r else None
+        d_cost = device.empty((1,), torch.float64)
+        rc = _lib.load().sfm_ba_residuals(
+            device.ptr(d_cam), device.ptr(d_pts), device.ptr(self.d_obs), device.ptr(self.d_cam_idx),
+            device.ptr(self.d_pt_idx), self.n_cams, self.n_pts, self.n_obs, _hptr(self.K),
+            device.ptr(d_r), device.ptr(d_cost), device.ptr(self.ws), self.ws_bytes, device.stream())
+        _lib.check(rc, "sfm_ba_residuals")
+        return d_r, d_cost
+
+    def solve_device(self, d_cam, d_pts, max_nfev=BA_MAX_NFEV, tol=REF_TOL, lambda0=1e-4, verbose=False):
+        """K8-K12 LM; d_cam [n_cams,6] and d_pts [n_pts,3] are refined in place. Returns a dict."""
+        lib = _lib.load()
+        opts = _lib.BAOptions()
+        lib.sfm_ba_default_options(C.addressof(opts))
+        opts.max_trials, opts.verbose = int(max_nfev), int(bool(verbose))
+        opts.ftol = opts.xtol = opts.gtol = float(tol)
+        opts.lambda0 = float(lambda0)
+        res = _lib.BAResult()
+        rc = lib.sfm_ba_solve(
+            device.ptr(d_cam), device.ptr(d_pts), device.ptr(self.d_obs), device.ptr(self.d_cam_idx),
+            device.ptr(self.d_pt_idx), self.n_cams, self.n_pts, self.n_obs, _hptr(self.K),
+            C.addressof(opts), C.addressof(res), device.ptr(self.ws), self.ws_bytes, device.stream())
+        _lib.check(rc, "sfm_ba_solve")
+        return dict(cost0=res.cost0, cost=res.cost, gnorm=res.gnorm, lambda_=res.lambda_, status=res.status,
+                    n_linearisations=res.n_linearisations, n_trials=res.n_trials, n_chol_fail=res.n_chol_fail)
+
+
+def ba_solve_sparse(cams, pts, cam_idx, pt_idx, obs, K, max_nfev=BA_MAX_NFEV, tol=REF_TOL, verbose=False):
+    """Host arrays in/out: cams [Nc,6] = [rotvec, t], pts [Np,3] -> (cams, pts, info)."""
+    cams = np.ascontiguousarray(cams, np.float64).reshape(-1, 6)
+    pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 3)
+    prob = BAProblem(len(cams), len(pts), cam_idx, pt_idx, obs, K)
+    d_cam, d_pts = device.to_device(cams), device.to_device(pts)
+    info = prob.solve_device(d_cam, d_pts, max_nfev, tol, verbose=verbose)
+    return d_cam.cpu().numpy(), d_pts.cpu().numpy(), info
+
+
+# ---------------------------------------------------------------------------------------------
+# BundleAdjustment.py names
+# ---------------------------------------------------------------------------------------------
+def project_points(K, C_, R, X):
+    """BundleAdjustment.py:8-40 (exported helper; a handful of points, host arithmetic)."""
+    K, C_, R, X = np.array(K, float), np.array(C_, float), np.array(R, float), np.array(X, float)
+    P = K @ np.hstack([R, -R @ C_.reshape(3, 1)])
+    xh = (P @ np.hstack([X, np.ones((X.shape[0], 1))]).T).T
+    return xh[:, :2] / (xh[:, 2:3] + 1e-8)
+
+
+def bundle_adjustment_residuals(params, n_cameras, n_points, camera_indices, point_indices, points_2d, K,
+                                n_cam_params=6):
+    """Drop-in for BundleAdjustment.py:43-110 -> residual vector (2*n_obs,), interleaved [du,dv],
+    observed - projected, in the caller's observation order. Evaluated by K8 on the GPU."""
+    if n_cam_params != 6:
+        raise ValueError("only the reference's 6-parameter camera block [rotvec, t] is supported")
+    params = np.asarray(params, np.float64)
+    cams = params[:n_cameras * 6].reshape(n_cameras, 6)
+    pts = params[n_cameras * 6:n_cameras * 6 + n_points * 3].reshape(n_points, 3)
+    cam_idx = np.ascontiguousarray(camera_indices, np.int32)
+    pt_idx = np.ascontiguousarray(point_indices, np.int32)
+    if len(cam_idx) == 0:
+        return np.array([])
+    # K8 has no ordering requirement, but BAProblem sorts by point: undo that for the caller
+    order = None
+    if len(pt_idx) > 1 and np.any(np.diff(pt_idx) < 0):
+        order = np.argsort(pt_idx, kind="stable")
+    prob = BAProblem(n_cameras, n_points, cam_idx, pt_idx, points_2d, K)
+    d_r, _ = prob.residuals_device(device.to_device(cams), device.to_device(pts))
+    r = d_r.cpu().numpy()
+    if order is not None:
+        out = np.empty_like(r)
+        out[order] = r
+        r = out
+    return r.reshape(-1)
+
+
+def build_problem(all_world_coords, filtered_world_coords, feature_x, feature_y, filtered_feature_flags,
+                  R_set, C_set):
+    """Observation list and initial parameters of BundleAdjustment.py:148-199, vectorised (the
+    reference's nested loops are O(Nobs * Np)). Returns None when there is nothing to optimise."""
+    filtered_world_coords = np.asarray(filtered_world_coords)
+    valid = np.where(filtered_world_coords.flatten() == 1)[0]                  # :149-150
+    if len(valid) == 0:
+        return None
+    n_cameras = len(R_set)                                                     # :156 (cam_index unused)
+    flags = np.asarray(filtered_feature_flags)[valid][:, :n_cameras] == 1
+    pt_local, cam = np.nonzero(flags)                                          # point-major, camera ascending
+    if len(cam) == 0:
+        return None
+    fx, fy = np.asarray(feature_x), np.asarray(feature_y)
+    rows = valid[pt_local]
+    obs = np.stack([fx[rows, cam], fy[rows, cam]], axis=1).astype(np.float64)
+    cams = np.empty((n_cameras, 6))
+    for i in range(n_cameras):
+        R = np.array(R_set[i])
+        Cc = np.array(C_set[i])
+        cams[i, :3] = Rotation.from_matrix(R).as_rotvec()                      # :188 (raises for det <= 0)
+        cams[i, 3:] = -R @ Cc                                                  # :191
+    pts = np.asarray(all_world_coords, np.float64)[valid].reshape(-1, 3).copy()
+    return dict(valid=valid, n_cameras=n_cameras, n_points=len(valid), cam_idx=cam.astype(np.int32),
+                pt_idx=pt_local.astype(np.int32), obs=obs, cams=cams, pts=pts)
+
+
+def perform_bundle_adjustment(all_world_coords, filtered_world_coords, feature_x, feature_y,
+                              filtered_feature_flags, R_set, C_set, K, cam_index, tol=REF_TOL, info=None):
+    """Drop-in for BundleAdjustment.py:113-242 -> (R_set_opt, C_set_opt, all_world_coords_opt)."""
+    prob = build_problem(all_world_coords, filtered_world_coords, feature_x, feature_y,
+                         filtered_feature_flags, R_set, C_set)
+    if prob is None:                                                           # :152-153, :171-172
+        return R_set, C_set, all_world_coords
+    n_cameras, n_points, n_obs = prob["n_cameras"], prob["n_points"], len(prob["cam_idx"])
+    print(f"  Bundle adjustment: {n_cameras} cameras, {n_points} points, {n_obs} observations")
+    try:
+        m, n = 2 * n_obs, 6 * n_cameras + 3 * n_points
+        if m < n:                                                              # scipy's check for 'lm'
+            raise ValueError("Method 'lm' doesn't work when the number of residuals is less than the "
+                             "number of variables.")
+        cams, pts, res = ba_solve_sparse(prob["cams"], prob["pts"], prob["cam_idx"], prob["pt_idx"],
+                                         prob["obs"], np.array(K, float), BA_MAX_NFEV, tol)
+        if res["status"] < 0:
+            raise ValueError("Residuals are not finite in the initial point.")
+        Rm = Rotation.from_rotvec(cams[:, :3]).as_matrix()
+        R_set_opt = [Rm[i] for i in range(n_cameras)]                          # :220-228
+        C_set_opt = [-Rm[i].T @ cams[i, 3:] for i in range(n_cameras)]
+        all_world_coords_opt = np.array(all_world_coords, copy=True)           # :231-234
+        all_world_coords_opt[prob["valid"]] = pts
+        print(f"  Bundle adjustment completed. Final cost: {res['cost']:.6f}")
+        if info is not None:
+            info.update(res, cams=cams, pts=pts)
+        return R_set_opt, C_set_opt, all_world_coords_opt
+    except _lib.SfmError:
+        raise                                  # a broken GPU path must fail loudly, not look like a BA failure
+    except Exception as e:                                                     # :240-242
+        print(f"  Bundle adjustment failed: {e}")
+        return R_set, C_set, all_world_coords

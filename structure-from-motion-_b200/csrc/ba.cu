@@ -1,0 +1,972 @@
+// ba.cu -- K8..K12: Schur-complement Levenberg-Marquardt bundle adjustment on the GPU.
+//
+// Replaces perform_bundle_adjustment's scipy least_squares(method='lm') call
+// (BundleAdjustment.py:205-212) and the residual it minimises (bundle_adjustment_residuals,
+// BundleAdjustment.py:43-110; project_points :8-40). Parameter layout, residual sign/order and
+// the +1e-8 denominator are the reference's (SURVEY.md 8.1-Q2,Q5); observations arrive sorted by
+// point (the reference's own order, BundleAdjustment.py:164-169).
+//
+// Kernel chain per LM linearisation:
+//   ba_cam_linearise   per camera: M = K R, K t, right Jacobian of SO(3)        (21 doubles)
+//   K9p point pass     thread per observation: residual, analytic 2x6 / 2x3 Jacobians;
+//                      W = Jc^T Jp streamed out as 18 coalesced planes; V = sum Jp^T Jp and
+//                      g_p = sum Jp^T r by a segmented warp reduction over the point-sorted
+//                      observations; 0.5|r|^2 into per-CTA partials (deterministic)
+//   K9c camera pass    the same residual re-evaluated in camera-major order (index built once
+//                      per problem): U = sum Jc^T Jc, g_c = sum Jc^T r per camera, block
+//                      reductions, no atomics
+// and per trial step (damping lambda):
+//   K10 schur          warp per point: (V + lambda Dp^2)^-1 in registers, Y = W V^-1,
+//                      S -= Y W^T (lower block triangle) and g_red -= Y g_p
+//   K11 chol_solve     blocked Cholesky + solve of S dc = g_red (chol.cu)
+//   K12 update         dp = V^-1 (g_p - W^T dc); trial parameters; predicted-reduction terms
+//   K8  cost pass      0.5 |r|^2 at the trial point
+// The LM controller (host, a few scalars per trial) uses MINPACK's scaling (D = running max of
+// the Jacobian column norms, scipy x_scale='jac'), MINPACK's gain-ratio acceptance and its
+// ftol / xtol / gtol stopping rules, with a direct damping update instead of lmpar's secular
+// equation: the problem has a 7-dof gauge freedom (no camera is fixed, BundleAdjustment.py:180-199),
+// so J is rank deficient and lmpar's trajectory is rounding noise; both converge to the same
+// minimum (DESIGN.md "BA").
+#include "ba_math.cuh"
+#include <cub/device/device_radix_sort.cuh>
+#include <stdio.h>
+#include <string.h>
+#include <algorithm>
+#include <vector>
+
+namespace sfm {
+
+int chol_solve_launch(double *A, size_t ld, int npad, double *d_Linv, double *d_x, int *d_fail,
+                      cudaStream_t st);
+constexpr int BA_NB = 48;                 // == CH_NB in chol.cu
+constexpr int BA_CHUNK = 2048;            // observations per camera-pass CTA
+constexpr size_t BA_SMEM_CAM_LIMIT = 200 * 1024;
+
+struct KParam { double k[9]; };
+
+// ------------------------------------------------------------------------------ small helpers
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// block-wide deterministic sum; result valid in thread 0. sbuf: >= 32 doubles.
+__device__ __forceinline__ double block_sum(double v, double *sbuf) {
+    v = warp_sum(v);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sbuf[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double s = 0.0;
+    if (threadIdx.x == 0)
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += sbuf[w];
+    return s;
+}
+
+// Segmented sum over lanes with equal (sorted, contiguous) key: afterwards the first lane of
+// every run holds the run's total.
+template <int N>
+__device__ __forceinline__ void seg_reduce(double (&v)[N], int key, int lane) {
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        int k2 = __shfl_down_sync(0xffffffffu, key, off);
+        bool take = (lane + off < 32) && (k2 == key);
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            double t = __shfl_down_sync(0xffffffffu, v[i], off);
+            if (take) v[i] += t;
+        }
+    }
+}
+
+__device__ __forceinline__ void atomic_max_pos(unsigned long long *addr, double v) {
+    // non-negative doubles order like their bit patterns
+    if (v > 0.0) atomicMax(addr, (unsigned long long)__double_as_longlong(v));
+}
+
+// ------------------------------------------------------------------------------ index building
+__global__ void ba_iota_kernel(int32_t *idx, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) idx[i] = i;
+}
+
+// CSR pointer from a sorted key array: ptr[k] = first position with key >= k, ptr[nkeys] = n.
+// Also validates range and order (flag |= 1 on violation).
+__global__ void ba_csr_from_sorted_kernel(const int32_t *__restrict__ keys, int n, int nkeys,
+                                          int32_t *__restrict__ ptr, int *__restrict__ flag) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n) return;
+    int prev = i == 0 ? -1 : keys[i - 1];
+    int cur = i == n ? nkeys : keys[i];
+    if (i < n && (cur < 0 || cur >= nkeys)) { atomicOr(flag, 1); return; }
+    if (i > 0 && i < n && cur < prev) { atomicOr(flag, 1); return; }
+    if (prev < 0) prev = -1;
+    for (int k = prev + 1; k <= cur && k <= nkeys; ++k) ptr[k] = i;
+}
+
+__global__ void ba_range_check_kernel(const int32_t *__restrict__ keys, int n, int nkeys, int *__restrict__ flag) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && (keys[i] < 0 || keys[i] >= nkeys)) atomicOr(flag, 1);
+}
+
+__global__ void ba_gather_cam_major_kernel(const int32_t *__restrict__ perm, const double2 *__restrict__ obs,
+                                           const int32_t *__restrict__ pt_idx, int n,
+                                           double2 *__restrict__ obs_c, int32_t *__restrict__ pt_c) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int o = perm[i];
+    obs_c[i] = obs[o];
+    pt_c[i] = pt_idx[o];
+}
+
+// ------------------------------------------------------------------------------ linearisation
+__global__ void ba_cam_linearise_kernel(KParam K, const double *__restrict__ cam, int nc,
+                                        double *__restrict__ camlin) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= nc) return;
+    CamLin cl;
+    cam_linearise(K.k, cam + 6 * (size_t)c, cl);
+    camlin_store(cl, camlin + (size_t)CAMLIN_STRIDE * c);
+}
+
+// K9p. Persistent grid; thread per observation (grid-stride in whole warps).
+template <bool SMEM_CAMS, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+ba_point_pass_kernel(KParam K, const double *__restrict__ camlin, int nc, const double *__restrict__ pts,
+                     const double2 *__restrict__ obs, const int32_t *__restrict__ cam_idx,
+                     const int32_t *__restrict__ pt_idx, const int32_t *__restrict__ pt_ptr, int nobs,
+                     double *__restrict__ W, double *__restrict__ V, double *__restrict__ gp,
+                     double *__restrict__ costpart) {
+    extern __shared__ double scam[];
+    __shared__ double sred[32];
+    const double *ctab = camlin;
+    if (SMEM_CAMS) {
+        for (int i = threadIdx.x; i < nc * CAMLIN_STRIDE; i += THREADS) scam[i] = camlin[i];
+        __syncthreads();
+        ctab = scam;
+    }
+    const int lane = threadIdx.x & 31;
+    double cost = 0.0;
+    const int stride = gridDim.x * THREADS;
+    const int nround = (nobs + 31) & ~31;
+    for (int o = blockIdx.x * THREADS + threadIdx.x; o < nround; o += stride) {
+        const bool active = o < nobs;
+        int p = -1;
+        double v[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) v[i] = 0.0;
+        if (active) {
+            const int c = cam_idx[o];
+            p = pt_idx[o];
+            const double2 ob = obs[o];
+            double X[3] = {pts[3 * (size_t)p], pts[3 * (size_t)p + 1], pts[3 * (size_t)p + 2]};
+            CamLin cl;
+            camlin_load(ctab + (size_t)CAMLIN_STRIDE * c, cl);
+            double ru, rv, jc[2][6], jp[2][3];
+            reproj_residual(cl, K.k, X, ob.x, ob.y, BA_EPS, ru, rv, jc, jp);
+            cost += 0.5 * (ru * ru + rv * rv);
+#pragma unroll
+            for (int r = 0; r < 6; ++r)
+#pragma unroll
+                for (int a = 0; a < 3; ++a)
+                    W[(size_t)(r * 3 + a) * nobs + o] = jc[0][r] * jp[0][a] + jc[1][r] * jp[1][a];
+            v[0] = jp[0][0] * jp[0][0] + jp[1][0] * jp[1][0];
+            v[1] = jp[0][1] * jp[0][0] + jp[1][1] * jp[1][0];
+            v[2] = jp[0][1] * jp[0][1] + jp[1][1] * jp[1][1];
+            v[3] = jp[0][2] * jp[0][0] + jp[1][2] * jp[1][0];
+            v[4] = jp[0][2] * jp[0][1] + jp[1][2] * jp[1][1];
+            v[5] = jp[0][2] * jp[0][2] + jp[1][2] * jp[1][2];
+            v[6] = jp[0][0] * ru + jp[1][0] * rv;
+            v[7] = jp[0][1] * ru + jp[1][1] * rv;
+            v[8] = jp[0][2] * ru + jp[1][2] * rv;
+        }
+        seg_reduce<9>(v, p, lane);
+        const int prev = __shfl_up_sync(0xffffffffu, p, 1);
+        const bool head = (lane == 0) || (prev != p);
+        if (head && p >= 0) {
+            const int seg_beg = pt_ptr[p], seg_end = pt_ptr[p + 1];
+            const bool complete = (o == seg_beg) && (seg_end <= o - lane + 32);
+            double *Vp = V + 6 * (size_t)p, *gpp = gp + 3 * (size_t)p;
+            if (complete) {
+#pragma unroll
+                for (int i = 0; i < 6; ++i) Vp[i] = v[i];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) gpp[i] = v[6 + i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 6; ++i) atomicAdd(Vp + i, v[i]);
+#pragma unroll
+                for (int i = 0; i < 3; ++i) atomicAdd(gpp + i, v[6 + i]);
+            }
+        }
+    }
+    double s = block_sum(cost, sred);
+    if (threadIdx.x == 0) costpart[blockIdx.x] = s;
+}
+
+// K8. Same traversal as K9p, residual only. r_out (may be null): [nobs,2] interleaved residuals.
+template <bool SMEM_CAMS, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+ba_cost_kernel(const double *__restrict__ camlin, int nc, const double *__restrict__ pts,
+               const double2 *__restrict__ obs, const int32_t *__restrict__ cam_idx,
+               const int32_t *__restrict__ pt_idx, int nobs, double *__restrict__ costpart,
+               double2 *__restrict__ r_out) {
+    extern __shared__ double scam[];
+    __shared__ double sred[32];
+    const double *ctab = camlin;
+    if (SMEM_CAMS) {
+        for (int i = threadIdx.x; i < nc * CAMLIN_STRIDE; i += THREADS) scam[i] = camlin[i];
+        __syncthreads();
+        ctab = scam;
+    }
+    double cost = 0.0;
+    const int stride = gridDim.x * THREADS;
+    for (int o = blockIdx.x * THREADS + threadIdx.x; o < nobs; o += stride) {
+        const int c = cam_idx[o], p = pt_idx[o];
+        const double2 ob = obs[o];
+        double X[3] = {pts[3 * (size_t)p], pts[3 * (size_t)p + 1], pts[3 * (size_t)p + 2]};
+        const double *cp = ctab + (size_t)CAMLIN_STRIDE * c;
+        CamLin cl;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) cl.M[i] = cp[i];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) cl.kt[i] = cp[9 + i];
+        double ru, rv;
+        ba_residual_only(cl, X, ob.x, ob.y, ru, rv);
+        cost += 0.5 * (ru * ru + rv * rv);
+        if (r_out) r_out[o] = make_double2(ru, rv);
+    }
+    double s = block_sum(cost, sred);
+    if (threadIdx.x == 0) costpart[blockIdx.x] = s;
+}
+
+// K9c. One CTA per (camera, chunk of its observations) in camera-major order.
+__global__ void __launch_bounds__(256)
+ba_camera_pass_kernel(KParam K, const double *__restrict__ camlin, const double *__restrict__ pts,
+                      const double2 *__restrict__ obs_c, const int32_t *__restrict__ pt_c,
+                      const int32_t *__restrict__ chunk_cam, const int32_t *__restrict__ chunk_beg,
+                      const int32_t *__restrict__ chunk_end, double *__restrict__ Upart) {
+    __shared__ double sred[8][27];
+    const int ch = blockIdx.x;
+    const int c = chunk_cam[ch], beg = chunk_beg[ch], end = chunk_end[ch];
+    CamLin cl;
+    camlin_load(camlin + (size_t)CAMLIN_STRIDE * c, cl);
+    double acc[27];
+#pragma unroll
+    for (int i = 0; i < 27; ++i) acc[i] = 0.0;
+    for (int o = beg + threadIdx.x; o < end; o += 256) {
+        const int p = pt_c[o];
+        const double2 ob = obs_c[o];
+        double X[3] = {pts[3 * (size_t)p], pts[3 * (size_t)p + 1], pts[3 * (size_t)p + 2]};
+        double ru, rv, jc[2][6], jp[2][3];
+        reproj_residual(cl, K.k, X, ob.x, ob.y, BA_EPS, ru, rv, jc, jp);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+            acc[21 + r] += jc[0][r] * ru + jc[1][r] * rv;
+#pragma unroll
+            for (int q = 0; q <= r; ++q) acc[sym_idx(r, q)] += jc[0][r] * jc[0][q] + jc[1][r] * jc[1][q];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 27; ++i) acc[i] = warp_sum(acc[i]);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < 27; ++i) sred[warp][i] = acc[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < 27) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += sred[w][threadIdx.x];
+        Upart[(size_t)ch * 27 + threadIdx.x] = s;
+    }
+}
+
+// Sum the chunk partials of every camera in chunk order -> U [nc,21], gc [nc,6]; update the
+// MINPACK scaling Dc (first linearisation: column norm, 1 if zero; later: running max) and
+// the gtol numerator max_j |g_j| / |J_j|.
+__global__ void ba_cam_finalize_kernel(const double *__restrict__ Upart, const int32_t *__restrict__ chunk_ptr,
+                                       int nc, int first, double *__restrict__ U, double *__restrict__ gc,
+                                       double *__restrict__ Dc, unsigned long long *__restrict__ gmax) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= nc) return;
+    double acc[27];
+#pragma unroll
+    for (int i = 0; i < 27; ++i) acc[i] = 0.0;
+    for (int ch = chunk_ptr[c]; ch < chunk_ptr[c + 1]; ++ch)
+#pragma unroll
+        for (int i = 0; i < 27; ++i) acc[i] += Upart[(size_t)ch * 27 + i];
+#pragma unroll
+    for (int i = 0; i < 21; ++i) U[(size_t)c * 21 + i] = acc[i];
+    double gm = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        gc[(size_t)c * 6 + j] = acc[21 + j];
+        double cn = sqrt(acc[sym_idx(j, j)]);
+        double d = first ? (cn == 0.0 ? 1.0 : cn) : fmax(Dc[(size_t)c * 6 + j], cn);
+        Dc[(size_t)c * 6 + j] = d;
+        if (cn > 0.0) gm = fmax(gm, fabs(acc[21 + j]) / cn);
+    }
+    atomic_max_pos(gmax, gm);
+}
+
+// ------------------------------------------------------------------------------ Schur complement
+// After the memset of S: diagonal blocks U_c + lambda Dc^2, right-hand-side row g_c, identity on
+// the padding diagonal.
+__global__ void ba_schur_init_kernel(const double *__restrict__ U, const double *__restrict__ gc,
+                                     const double *__restrict__ Dc, int nc, int npad, size_t ld,
+                                     double lambda, double *__restrict__ S) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = 6 * nc;
+    if (t < nc * 36) {
+        int c = t / 36, e = t - 36 * c, r = e / 6, q = e - 6 * r;
+        double v = U[(size_t)c * 21 + sym_idx(r, q)];
+        if (r == q) {
+            double d = Dc[(size_t)c * 6 + r];
+            v += lambda * d * d;
+        }
+        S[(size_t)(6 * c + r) * ld + 6 * c + q] = v;
+    }
+    if (t < n) S[(size_t)npad * ld + t] = gc[t];
+    if (t >= n && t < npad) S[(size_t)t * ld + t] = 1.0;
+}
+
+constexpr int SCH_KT = 32;      // observations per point on the shared-memory path
+constexpr int SCH_WARPS = 4;
+
+__device__ __forceinline__ double sym3_at(const double *s, int r, int c) { return s[sym_idx(r, c)]; }
+
+// K10: warp per point.
+__global__ void __launch_bounds__(SCH_WARPS * 32)
+ba_schur_kernel(const double *__restrict__ W, int nobs, const int32_t *__restrict__ cam_idx,
+                const int32_t *__restrict__ pt_ptr, int npts, const double *__restrict__ V,
+                const double *__restrict__ gp, double *__restrict__ Dp, double lambda, int update_D,
+                int first, double *__restrict__ Vinv, double *__restrict__ bp, double *__restrict__ S,
+                size_t ld, double *__restrict__ gred, unsigned long long *__restrict__ gmax,
+                int *__restrict__ fail) {
+    __shared__ double sW[SCH_WARPS][SCH_KT * 18];
+    __shared__ double sY[SCH_WARPS][SCH_KT * 18];
+    __shared__ int sC[SCH_WARPS][SCH_KT];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *w_ = sW[warp], *y_ = sY[warp];
+    int *c_ = sC[warp];
+    for (int p = blockIdx.x * SCH_WARPS + warp; p < npts; p += gridDim.x * SCH_WARPS) {
+        double v[6], g[3], d[3];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) v[i] = V[6 * (size_t)p + i];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) g[i] = gp[3 * (size_t)p + i];
+        if (update_D) {
+            double gm = 0.0;
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                double cn = sqrt(v[sym_idx(j, j)]);
+                d[j] = first ? (cn == 0.0 ? 1.0 : cn) : fmax(Dp[3 * (size_t)p + j], cn);
+                if (cn > 0.0) gm = fmax(gm, fabs(g[j]) / cn);
+            }
+            if (lane == 0) {
+#pragma unroll
+                for (int j = 0; j < 3; ++j) Dp[3 * (size_t)p + j] = d[j];
+                atomic_max_pos(gmax, gm);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) d[j] = Dp[3 * (size_t)p + j];
+        }
+        __syncwarp();
+        v[0] += lambda * d[0] * d[0];
+        v[2] += lambda * d[1] * d[1];
+        v[5] += lambda * d[2] * d[2];
+        double vi[6];
+        if (!spd3_inverse(v, vi)) {
+            if (lane == 0) atomicOr(fail, 2);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) vi[i] = 0.0;
+        }
+        double b[3];
+        sym3_mul(vi, g, b);
+        if (lane == 0) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) Vinv[6 * (size_t)p + i] = vi[i];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) bp[3 * (size_t)p + i] = b[i];
+        }
+        const int o0 = pt_ptr[p], k = pt_ptr[p + 1] - o0;
+        if (k <= 0) continue;
+        if (k <= SCH_KT) {
+            for (int e = lane; e < 18 * k; e += 32) {
+                int rc = e / k, i = e - rc * k;
+                w_[i * 18 + rc] = W[(size_t)rc * nobs + o0 + i];
+            }
+            for (int i = lane; i < k; i += 32) c_[i] = cam_idx[o0 + i];
+            __syncwarp();
+            for (int e = lane; e < 6 * k; e += 32) {
+                int i = e / 6, r = e - 6 * i;
+                double w0 = w_[i * 18 + 3 * r], w1 = w_[i * 18 + 3 * r + 1], w2 = w_[i * 18 + 3 * r + 2];
+                y_[i * 18 + 3 * r + 0] = w0 * vi[0] + w1 * vi[1] + w2 * vi[3];
+                y_[i * 18 + 3 * r + 1] = w0 * vi[1] + w1 * vi[2] + w2 * vi[4];
+                y_[i * 18 + 3 * r + 2] = w0 * vi[3] + w1 * vi[4] + w2 * vi[5];
+                atomicAdd(&gred[6 * c_[i] + r], -(w0 * b[0] + w1 * b[1] + w2 * b[2]));
+            }
+            __syncwarp();
+            for (int i = 0; i < k; ++i) {
+                const int ci = c_[i];
+                for (int idx = lane; idx < (i + 1) * 36; idx += 32) {
+                    int j = idx / 36, el = idx - 36 * j, r = el / 6, q = el - 6 * r;
+                    const int cj = c_[j];
+                    const double *yr = y_ + i * 18 + 3 * r, *wq = w_ + j * 18 + 3 * q;
+                    double val = -(yr[0] * wq[0] + yr[1] * wq[1] + yr[2] * wq[2]);
+                    if (ci > cj || j == i) {
+                        atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * cj + q], val);
+                    } else if (ci < cj) {
+                        atomicAdd(&S[(size_t)(6 * cj + q) * ld + 6 * ci + r], val);
+                    } else {   // the same camera twice on one point: both orders land in the block
+                        atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * ci + q], val);
+                        atomicAdd(&S[(size_t)(6 * ci + q) * ld + 6 * ci + r], val);
+                    }
+                }
+            }
+            __syncwarp();
+        } else {
+            // long tracks: same arithmetic straight from global memory (L1/L2 resident)
+            for (int e = lane; e < 6 * k; e += 32) {
+                int i = e / 6, r = e - 6 * i;
+                size_t o = (size_t)o0 + i;
+                double w0 = W[(size_t)(3 * r) * nobs + o], w1 = W[(size_t)(3 * r + 1) * nobs + o],
+                       w2 = W[(size_t)(3 * r + 2) * nobs + o];
+                atomicAdd(&gred[6 * cam_idx[o] + r], -(w0 * b[0] + w1 * b[1] + w2 * b[2]));
+            }
+            for (int i = 0; i < k; ++i) {
+                const int ci = cam_idx[o0 + i];
+                for (long long idx = lane; idx < (long long)(i + 1) * 36; idx += 32) {
+                    int j = (int)(idx / 36), el = (int)(idx - 36LL * j), r = el / 6, q = el - 6 * r;
+                    const int cj = cam_idx[o0 + j];
+                    size_t oi = (size_t)o0 + i, oj = (size_t)o0 + j;
+                    double w0 = W[(size_t)(3 * r) * nobs + oi], w1 = W[(size_t)(3 * r + 1) * nobs + oi],
+                           w2 = W[(size_t)(3 * r + 2) * nobs + oi];
+                    double y0 = w0 * vi[0] + w1 * vi[1] + w2 * vi[3];
+                    double y1 = w0 * vi[1] + w1 * vi[2] + w2 * vi[4];
+                    double y2 = w0 * vi[3] + w1 * vi[4] + w2 * vi[5];
+                    double val = -(y0 * W[(size_t)(3 * q) * nobs + oj] + y1 * W[(size_t)(3 * q + 1) * nobs + oj] +
+                                   y2 * W[(size_t)(3 * q + 2) * nobs + oj]);
+                    if (ci > cj || j == i) {
+                        atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * cj + q], val);
+                    } else if (ci < cj) {
+                        atomicAdd(&S[(size_t)(6 * cj + q) * ld + 6 * ci + r], val);
+                    } else {
+                        atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * ci + q], val);
+                        atomicAdd(&S[(size_t)(6 * ci + q) * ld + 6 * ci + r], val);
+                    }
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------ update (K12)
+// partial sums layout (4 doubles): [s.g, |D s|^2, |D x_new|^2, |D x_cur|^2]
+__global__ void __launch_bounds__(256)
+ba_update_cams_kernel(const double *__restrict__ cam, const double *__restrict__ dc, const double *__restrict__ gc,
+                      const double *__restrict__ Dc, int n, double *__restrict__ cam_new,
+                      double *__restrict__ part) {
+    __shared__ double sred[32];
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    for (int j = threadIdx.x; j < n; j += 256) {
+        double s = dc[j], x = cam[j], xn = x - s, d = Dc[j];
+        cam_new[j] = xn;
+        a0 += s * gc[j];
+        a1 += (d * s) * (d * s);
+        a2 += (d * xn) * (d * xn);
+        a3 += (d * x) * (d * x);
+    }
+    a0 = block_sum(a0, sred); a1 = block_sum(a1, sred); a2 = block_sum(a2, sred); a3 = block_sum(a3, sred);
+    if (threadIdx.x == 0) { part[0] = a0; part[1] = a1; part[2] = a2; part[3] = a3; }
+}
+
+// tp[p] = sum over the observations of p of W_o^T dc[cam(o)]   (thread per observation)
+__global__ void __launch_bounds__(256)
+ba_point_rhs_kernel(const double *__restrict__ W, int nobs, const int32_t *__restrict__ cam_idx,
+                    const int32_t *__restrict__ pt_idx, const int32_t *__restrict__ pt_ptr,
+                    const double *__restrict__ dc, double *__restrict__ tp) {
+    const int lane = threadIdx.x & 31;
+    const int o = blockIdx.x * 256 + threadIdx.x;
+    int p = -1;
+    double t[3] = {0.0, 0.0, 0.0};
+    if (o < nobs) {
+        p = pt_idx[o];
+        const double *s = dc + 6 * (size_t)cam_idx[o];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+            double sr = s[r];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) t[a] = fma(W[(size_t)(r * 3 + a) * nobs + o], sr, t[a]);
+        }
+    }
+    seg_reduce<3>(t, p, lane);
+    const int prev = __shfl_up_sync(0xffffffffu, p, 1);
+    const bool head = (lane == 0) || (prev != p);
+    if (head && p >= 0) {
+        const bool complete = (o == pt_ptr[p]) && (pt_ptr[p + 1] <= o - lane + 32);
+        double *dst = tp + 3 * (size_t)p;
+        if (complete) { dst[0] = t[0]; dst[1] = t[1]; dst[2] = t[2]; }
+        else { atomicAdd(dst, t[0]); atomicAdd(dst + 1, t[1]); atomicAdd(dst + 2, t[2]); }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+ba_update_points_kernel(const double *__restrict__ pts, const double *__restrict__ Vinv,
+                        const double *__restrict__ bp, const double *__restrict__ tp,
+                        const double *__restrict__ gp, const double *__restrict__ Dp, int npts,
+                        double *__restrict__ pts_new, double *__restrict__ part) {
+    __shared__ double sred[32];
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    for (int p = blockIdx.x * 256 + threadIdx.x; p < npts; p += gridDim.x * 256) {
+        double vi[6], t[3], vt[3];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) vi[i] = Vinv[6 * (size_t)p + i];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) t[i] = tp[3 * (size_t)p + i];
+        sym3_mul(vi, t, vt);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            double s = bp[3 * (size_t)p + i] - vt[i];
+            double x = pts[3 * (size_t)p + i], xn = x - s, d = Dp[3 * (size_t)p + i];
+            pts_new[3 * (size_t)p + i] = xn;
+            a0 += s * gp[3 * (size_t)p + i];
+            a1 += (d * s) * (d * s);
+            a2 += (d * xn) * (d * xn);
+            a3 += (d * x) * (d * x);
+        }
+    }
+    a0 = block_sum(a0, sred); a1 = block_sum(a1, sred); a2 = block_sum(a2, sred); a3 = block_sum(a3, sred);
+    if (threadIdx.x == 0) {
+        double *dst = part + 4 * (size_t)(blockIdx.x + 1);     // slot 0 belongs to the cameras
+        dst[0] = a0; dst[1] = a1; dst[2] = a2; dst[3] = a3;
+    }
+}
+
+// out[0] = sum costpart; out[1..4] = sum of the update partials; out[5] = gmax; out[6] = flags
+__global__ void __launch_bounds__(256)
+ba_reduce_scalars_kernel(const double *__restrict__ costpart, int ncost, const double *__restrict__ updpart,
+                         int nupd, const unsigned long long *__restrict__ gmax, const int *__restrict__ fail_s,
+                         const int *__restrict__ fail_c, double *__restrict__ out) {
+    __shared__ double sred[32];
+    double c = 0.0, a[4] = {0, 0, 0, 0};
+    for (int i = threadIdx.x; i < ncost; i += 256) c += costpart[i];
+    for (int i = threadIdx.x; i < nupd; i += 256)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) a[q] += updpart[4 * (size_t)i + q];
+    c = block_sum(c, sred);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) a[q] = block_sum(a[q], sred);
+    if (threadIdx.x == 0) {
+        out[0] = c;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) out[1 + q] = a[q];
+        out[5] = gmax ? __longlong_as_double((long long)*gmax) : 0.0;
+        out[6] = (double)((fail_s ? *fail_s : 0) | (fail_c ? (*fail_c ? 4 : 0) : 0));
+    }
+}
+
+// ------------------------------------------------------------------------------ host driver
+struct BAPlan {
+    int nc, np, nobs, npad, nchunks, grid_obs, grid_pts, obs_threads;
+    bool smem_cams;
+    size_t ld, cam_smem;
+    // index structures
+    int32_t *pt_ptr, *cam_ptr, *perm, *keys_sorted, *iota, *pt_c, *chunk_cam, *chunk_beg, *chunk_end, *chunk_ptr;
+    double2 *obs_c;
+    void *cub_tmp;
+    size_t cub_bytes;
+    // state
+    double *cam[2], *pts[2], *camlin[2];
+    double *W, *V, *gp, *Vinv, *bp, *tp, *U, *gc, *Upart, *Dc, *Dp, *S, *Linv, *dc;
+    double *costpart, *updpart, *scal;
+    unsigned long long *gmax;
+    int *flags;       // [0] index validation, [1] schur (vinv) failure, [2] cholesky failure
+};
+
+static size_t carve(unsigned char *&p, size_t bytes) {
+    size_t off = (size_t)p;
+    p += align_up(bytes, 256);
+    return off;
+}
+
+static size_t cub_sort_bytes(int nobs, int nc) {
+    size_t bytes = 0;
+    int bits = 1;
+    while ((1 << bits) < nc && bits < 31) ++bits;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const int32_t *)nullptr, (int32_t *)nullptr,
+                                    (const int32_t *)nullptr, (int32_t *)nullptr, nobs, 0, bits);
+    return bytes;
+}
+
+// Lays the plan out over a workspace starting at `base` (base == nullptr: size query only).
+static size_t ba_layout(BAPlan &pl, unsigned char *base, int nc, int np, int nobs) {
+    unsigned char *p = base;
+    pl.nc = nc; pl.np = np; pl.nobs = nobs;
+    pl.npad = ceil_div(6 * nc, BA_NB) * BA_NB;
+    pl.ld = (size_t)pl.npad;
+    const int sms = sm_count();
+    pl.cam_smem = (size_t)nc * CAMLIN_STRIDE * sizeof(double);
+    pl.smem_cams = pl.cam_smem <= BA_SMEM_CAM_LIMIT;
+    pl.obs_threads = (pl.smem_cams && pl.cam_smem > 100 * 1024) ? 512 : 256;
+    int per_sm = pl.obs_threads == 512 ? 1 : 2;
+    pl.grid_obs = std::max(1, std::min(sms * per_sm, ceil_div(nobs, pl.obs_threads)));
+    pl.grid_pts = std::max(1, std::min(sms * 4, ceil_div(np, 256)));
+    const int max_chunks = nobs / BA_CHUNK + nc + 1;
+    const size_t D = sizeof(double), I = sizeof(int32_t);
+#define CARVE(field, type, count) pl.field = reinterpret_cast<type *>(carve(p, (size_t)(count)))
+    CARVE(pt_ptr, int32_t, I * (np + 1));
+    CARVE(cam_ptr, int32_t, I * (nc + 1));
+    CARVE(perm, int32_t, I * nobs);
+    CARVE(keys_sorted, int32_t, I * nobs);
+    CARVE(iota, int32_t, I * nobs);
+    CARVE(pt_c, int32_t, I * nobs);
+    CARVE(chunk_cam, int32_t, I * max_chunks);
+    CARVE(chunk_beg, int32_t, I * max_chunks);
+    CARVE(chunk_end, int32_t, I * max_chunks);
+    CARVE(chunk_ptr, int32_t, I * (nc + 1));
+    CARVE(obs_c, double2, sizeof(double2) * nobs);
+    pl.cub_bytes = cub_sort_bytes(nobs, nc);
+    CARVE(cub_tmp, unsigned char, pl.cub_bytes + 256);
+    for (int i = 0; i < 2; ++i) {
+        CARVE(cam[i], double, D * 6 * nc);
+        CARVE(pts[i], double, D * 3 * np);
+        CARVE(camlin[i], double, D * CAMLIN_STRIDE * nc);
+    }
+    CARVE(W, double, D * 18 * nobs);
+    CARVE(V, double, D * 9 * np);        // V [np,6] immediately followed by gp [np,3]: one memset
+    pl.gp = pl.V + 6 * (size_t)np;
+    CARVE(Vinv, double, D * 6 * np);
+    CARVE(bp, double, D * 3 * np);
+    CARVE(tp, double, D * 3 * np);
+    CARVE(U, double, D * 21 * nc);
+    CARVE(gc, double, D * 6 * nc);
+    CARVE(Upart, double, D * 27 * max_chunks);
+    CARVE(Dc, double, D * 6 * nc);
+    CARVE(Dp, double, D * 3 * np);
+    CARVE(S, double, D * (pl.npad + BA_NB) * pl.ld);
+    CARVE(Linv, double, D * (pl.npad / BA_NB) * BA_NB * BA_NB);
+    CARVE(dc, double, D * pl.npad);
+    CARVE(costpart, double, D * (pl.grid_obs + 8));
+    CARVE(updpart, double, D * 4 * (pl.grid_pts + 2));
+    CARVE(scal, double, D * 16);
+    CARVE(gmax, unsigned long long, 8);
+    CARVE(flags, int, 64);
+#undef CARVE
+    return (size_t)(p - base);
+}
+
+template <bool SM>
+static void set_obs_kernel_attrs(size_t smem) {
+    cudaFuncSetAttribute(ba_point_pass_kernel<SM, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(ba_point_pass_kernel<SM, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(ba_cost_kernel<SM, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(ba_cost_kernel<SM, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+}
+
+static int launch_point_pass(const BAPlan &pl, const KParam &K, int cur, const double2 *obs,
+                             const int32_t *cam_idx, const int32_t *pt_idx, cudaStream_t st) {
+    SFM_CUDA_TRY(cudaMemsetAsync(pl.V, 0, sizeof(double) * 9 * (size_t)pl.np, st));
+    const size_t sm = pl.smem_cams ? pl.cam_smem : 0;
+#define PP_ARGS K, pl.camlin[cur], pl.nc, pl.pts[cur], obs, cam_idx, pt_idx, pl.pt_ptr, pl.nobs, pl.W, pl.V, pl.gp, pl.costpart
+    if (pl.smem_cams) {
+        if (pl.obs_threads == 512) ba_point_pass_kernel<true, 512, 1><<<pl.grid_obs, 512, sm, st>>>(PP_ARGS);
+        else ba_point_pass_kernel<true, 256, 2><<<pl.grid_obs, 256, sm, st>>>(PP_ARGS);
+    } else {
+        ba_point_pass_kernel<false, 256, 2><<<pl.grid_obs, 256, 0, st>>>(PP_ARGS);
+    }
+#undef PP_ARGS
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+static int launch_cost(const BAPlan &pl, const double *camlin, const double *pts, const double2 *obs,
+                       const int32_t *cam_idx, const int32_t *pt_idx, double2 *r_out, cudaStream_t st) {
+    const size_t sm = pl.smem_cams ? pl.cam_smem : 0;
+#define C_ARGS camlin, pl.nc, pts, obs, cam_idx, pt_idx, pl.nobs, pl.costpart, r_out
+    if (pl.smem_cams) {
+        if (pl.obs_threads == 512) ba_cost_kernel<true, 512, 1><<<pl.grid_obs, 512, sm, st>>>(C_ARGS);
+        else ba_cost_kernel<true, 256, 2><<<pl.grid_obs, 256, sm, st>>>(C_ARGS);
+    } else {
+        ba_cost_kernel<false, 256, 2><<<pl.grid_obs, 256, 0, st>>>(C_ARGS);
+    }
+#undef C_ARGS
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+static int launch_cam_linearise(const BAPlan &pl, const KParam &K, const double *cam, double *camlin,
+                                cudaStream_t st) {
+    ba_cam_linearise_kernel<<<ceil_div(pl.nc, 128), 128, 0, st>>>(K, cam, pl.nc, camlin);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+// Builds pt_ptr, the camera-major copy of the observations and the chunk table. Synchronises
+// the stream once (the chunk table is laid out on the host from the per-camera counts).
+static int ba_build_index(BAPlan &pl, const double2 *obs, const int32_t *cam_idx, const int32_t *pt_idx,
+                          cudaStream_t st) {
+    const int nobs = pl.nobs, nc = pl.nc, np = pl.np;
+    SFM_CUDA_TRY(cudaMemsetAsync(pl.flags, 0, 64 * sizeof(int), st));
+    ba_csr_from_sorted_kernel<<<ceil_div(nobs + 1, 256), 256, 0, st>>>(pt_idx, nobs, np, pl.pt_ptr, pl.flags);
+    SFM_LAUNCH_CHECK();
+    ba_range_check_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(cam_idx, nobs, nc, pl.flags);
+    SFM_LAUNCH_CHECK();
+    ba_iota_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(pl.iota, nobs);
+    SFM_LAUNCH_CHECK();
+    int bits = 1;
+    while ((1 << bits) < nc && bits < 31) ++bits;
+    size_t tmp = pl.cub_bytes;
+    SFM_CUDA_TRY(cub::DeviceRadixSort::SortPairs(pl.cub_tmp, tmp, cam_idx, pl.keys_sorted,
+                                                 (const int32_t *)pl.iota, pl.perm, nobs, 0, bits, st));
+    count_launch();
+    ba_csr_from_sorted_kernel<<<ceil_div(nobs + 1, 256), 256, 0, st>>>(pl.keys_sorted, nobs, nc, pl.cam_ptr,
+                                                                        pl.flags + 3);
+    SFM_LAUNCH_CHECK();
+    ba_gather_cam_major_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(pl.perm, obs, pt_idx, nobs, pl.obs_c, pl.pt_c);
+    SFM_LAUNCH_CHECK();
+    // chunk table on the host
+    std::vector<int32_t> cam_ptr(nc + 1);
+    int flag0 = 0;
+    SFM_CUDA_TRY(cudaMemcpyAsync(cam_ptr.data(), pl.cam_ptr, sizeof(int32_t) * (nc + 1), cudaMemcpyDeviceToHost, st));
+    SFM_CUDA_TRY(cudaMemcpyAsync(&flag0, pl.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+    SFM_CUDA_TRY(cudaStreamSynchronize(st));
+    if (flag0) return SFM_E_INVALID;        // indices out of range or not sorted by point
+    std::vector<int32_t> ccam, cbeg, cend, cptr(nc + 1);
+    for (int c = 0; c < nc; ++c) {
+        cptr[c] = (int32_t)ccam.size();
+        for (int b = cam_ptr[c]; b < cam_ptr[c + 1]; b += BA_CHUNK) {
+            ccam.push_back(c);
+            cbeg.push_back(b);
+            cend.push_back(std::min(b + BA_CHUNK, cam_ptr[c + 1]));
+        }
+    }
+    cptr[nc] = (int32_t)ccam.size();
+    pl.nchunks = (int)ccam.size();
+    if (pl.nchunks) {
+        SFM_CUDA_TRY(cudaMemcpyAsync(pl.chunk_cam, ccam.data(), sizeof(int32_t) * pl.nchunks, cudaMemcpyHostToDevice, st));
+        SFM_CUDA_TRY(cudaMemcpyAsync(pl.chunk_beg, cbeg.data(), sizeof(int32_t) * pl.nchunks, cudaMemcpyHostToDevice, st));
+        SFM_CUDA_TRY(cudaMemcpyAsync(pl.chunk_end, cend.data(), sizeof(int32_t) * pl.nchunks, cudaMemcpyHostToDevice, st));
+    }
+    SFM_CUDA_TRY(cudaMemcpyAsync(pl.chunk_ptr, cptr.data(), sizeof(int32_t) * (nc + 1), cudaMemcpyHostToDevice, st));
+    SFM_CUDA_TRY(cudaStreamSynchronize(st));   // the host vectors go out of scope
+    return SFM_OK;
+}
+
+}  // namespace sfm
+
+using namespace sfm;
+
+extern "C" void sfm_ba_default_options(sfm_ba_options *o) {
+    if (!o) return;
+    o->max_trials = 100;     // BundleAdjustment.py:211 max_nfev=100
+    o->verbose = 0;
+    o->ftol = o->xtol = o->gtol = 1e-8;   // scipy least_squares defaults
+    o->lambda0 = 1e-4;
+}
+
+extern "C" size_t sfm_ba_workspace_bytes(int32_t n_cams, int32_t n_pts, int32_t n_obs) {
+    if (n_cams < 1 || n_pts < 1 || n_obs < 1) return 0;
+    BAPlan pl;
+    return ba_layout(pl, nullptr, n_cams, n_pts, n_obs) + 256;
+}
+
+static bool g_attrs_set = false;
+
+static int ba_prepare(BAPlan &pl, void *d_ws, size_t ws_bytes, int32_t n_cams, int32_t n_pts, int32_t n_obs) {
+    if (n_cams < 1 || n_pts < 1 || n_obs < 1 || !d_ws) return SFM_E_INVALID;
+    unsigned char *base = reinterpret_cast<unsigned char *>(align_up((size_t)d_ws, 256));
+    size_t need = ba_layout(pl, base, n_cams, n_pts, n_obs);
+    if ((size_t)(base - (unsigned char *)d_ws) + need > ws_bytes) return SFM_E_WORKSPACE;
+    if (!g_attrs_set) {
+        set_obs_kernel_attrs<true>(BA_SMEM_CAM_LIMIT);
+        (void)cudaGetLastError();
+        g_attrs_set = true;
+    }
+    return SFM_OK;
+}
+
+extern "C" int sfm_ba_residuals(const double *d_cam, const double *d_pts, const double *d_obs,
+                                const int32_t *d_cam_idx, const int32_t *d_pt_idx, int32_t n_cams,
+                                int32_t n_pts, int32_t n_obs, const double *h_K, double *d_r,
+                                double *d_cost, void *d_ws, size_t ws_bytes, void *stream) {
+    if (!d_cam || !d_pts || !d_obs || !d_cam_idx || !d_pt_idx || !h_K) return SFM_E_INVALID;
+    BAPlan pl;
+    int rc = ba_prepare(pl, d_ws, ws_bytes, n_cams, n_pts, n_obs);
+    if (rc != SFM_OK) return rc;
+    cudaStream_t st = as_stream(stream);
+    KParam K;
+    for (int i = 0; i < 9; ++i) K.k[i] = h_K[i];
+    SFM_CUDA_TRY(cudaMemsetAsync(pl.flags, 0, 64 * sizeof(int), st));
+    ba_range_check_kernel<<<ceil_div(n_obs, 256), 256, 0, st>>>(d_cam_idx, n_obs, n_cams, pl.flags);
+    SFM_LAUNCH_CHECK();
+    ba_range_check_kernel<<<ceil_div(n_obs, 256), 256, 0, st>>>(d_pt_idx, n_obs, n_pts, pl.flags);
+    SFM_LAUNCH_CHECK();
+    int flag = 0;
+    SFM_CUDA_TRY(cudaMemcpyAsync(&flag, pl.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
+    SFM_CUDA_TRY(cudaStreamSynchronize(st));
+    if (flag) return SFM_E_INVALID;
+    if ((rc = launch_cam_linearise(pl, K, d_cam, pl.camlin[0], st)) != SFM_OK) return rc;
+    if ((rc = launch_cost(pl, pl.camlin[0], d_pts, reinterpret_cast<const double2 *>(d_obs), d_cam_idx,
+                          d_pt_idx, reinterpret_cast<double2 *>(d_r), st)) != SFM_OK) return rc;
+    ba_reduce_scalars_kernel<<<1, 256, 0, st>>>(pl.costpart, pl.grid_obs, nullptr, 0, nullptr, nullptr, nullptr,
+                                                pl.scal);
+    SFM_LAUNCH_CHECK();
+    if (d_cost) SFM_CUDA_TRY(cudaMemcpyAsync(d_cost, pl.scal, sizeof(double), cudaMemcpyDeviceToDevice, st));
+    return SFM_OK;
+}
+
+extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, const int32_t *d_cam_idx,
+                            const int32_t *d_pt_idx, int32_t n_cams, int32_t n_pts, int32_t n_obs,
+                            const double *h_K, const sfm_ba_options *opts, sfm_ba_result *h_result,
+                            void *d_ws, size_t ws_bytes, void *stream) {
+    if (!d_cam || !d_pts || !d_obs || !d_cam_idx || !d_pt_idx || !h_K || !h_result) return SFM_E_INVALID;
+    sfm_ba_options o;
+    if (opts) o = *opts; else sfm_ba_default_options(&o);
+    BAPlan pl;
+    int rc = ba_prepare(pl, d_ws, ws_bytes, n_cams, n_pts, n_obs);
+    if (rc != SFM_OK) return rc;
+    cudaStream_t st = as_stream(stream);
+    KParam K;
+    for (int i = 0; i < 9; ++i) K.k[i] = h_K[i];
+    const double2 *obs = reinterpret_cast<const double2 *>(d_obs);
+    memset(h_result, 0, sizeof(*h_result));
+    h_result->status = -1;
+
+    if ((rc = ba_build_index(pl, obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return rc;
+    const int nc = pl.nc, np = pl.np, nobs = pl.nobs, n = 6 * nc;
+    SFM_CUDA_TRY(cudaMemcpyAsync(pl.cam[0], d_cam, sizeof(double) * 6 * nc, cudaMemcpyDeviceToDevice, st));
+    SFM_CUDA_TRY(cudaMemcpyAsync(pl.pts[0], d_pts, sizeof(double) * 3 * (size_t)np, cudaMemcpyDeviceToDevice, st));
+    int cur = 0;
+    double *h_scal = nullptr;
+    SFM_CUDA_TRY(cudaMallocHost(&h_scal, 16 * sizeof(double)));
+    struct Pinned { double *p; ~Pinned() { cudaFreeHost(p); } } pinned{h_scal};
+
+    auto linearise = [&](int first) -> int {
+        int r;
+        SFM_CUDA_TRY(cudaMemsetAsync(pl.gmax, 0, 8, st));
+        if ((r = launch_point_pass(pl, K, cur, obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return r;
+        if (pl.nchunks) {
+            ba_camera_pass_kernel<<<pl.nchunks, 256, 0, st>>>(K, pl.camlin[cur], pl.pts[cur], pl.obs_c, pl.pt_c,
+                                                              pl.chunk_cam, pl.chunk_beg, pl.chunk_end, pl.Upart);
+            SFM_LAUNCH_CHECK();
+        }
+        ba_cam_finalize_kernel<<<ceil_div(nc, 128), 128, 0, st>>>(pl.Upart, pl.chunk_ptr, nc, first, pl.U, pl.gc,
+                                                                  pl.Dc, pl.gmax);
+        SFM_LAUNCH_CHECK();
+        return SFM_OK;
+    };
+
+    if ((rc = launch_cam_linearise(pl, K, pl.cam[0], pl.camlin[0], st)) != SFM_OK) return rc;
+    if ((rc = linearise(1)) != SFM_OK) return rc;
+    ba_reduce_scalars_kernel<<<1, 256, 0, st>>>(pl.costpart, pl.grid_obs, nullptr, 0, nullptr, nullptr, nullptr, pl.scal);
+    SFM_LAUNCH_CHECK();
+    SFM_CUDA_TRY(cudaMemcpyAsync(h_scal, pl.scal, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    SFM_CUDA_TRY(cudaStreamSynchronize(st));
+    double cost = h_scal[0];
+    h_result->cost0 = h_result->cost = cost;
+    h_result->n_linearisations = 1;
+    if (!(cost <= 1.7e308)) {            // NaN or inf: scipy raises, the reference returns its inputs
+        h_result->status = -1;
+        return SFM_OK;
+    }
+
+    double lambda = o.lambda0 > 0 ? o.lambda0 : 1e-4, nu = 2.0, xnorm = 0.0;
+    int status = -2, trials = 0, first_lin = 1, update_D = 1, chol_fail = 0;
+    const size_t s_bytes = sizeof(double) * (size_t)(pl.npad + BA_NB) * pl.ld;
+    while (status == -2) {
+        // ---- one trial step with damping lambda ----
+        SFM_CUDA_TRY(cudaMemsetAsync(pl.S, 0, s_bytes, st));
+        SFM_CUDA_TRY(cudaMemsetAsync(pl.flags + 1, 0, 2 * sizeof(int), st));
+        SFM_CUDA_TRY(cudaMemsetAsync(pl.tp, 0, sizeof(double) * 3 * (size_t)np, st));
+        ba_schur_init_kernel<<<ceil_div(std::max(nc * 36, pl.npad), 256), 256, 0, st>>>(pl.U, pl.gc, pl.Dc, nc, pl.npad,
+                                                                                       pl.ld, lambda, pl.S);
+        SFM_LAUNCH_CHECK();
+        {
+            int grid = std::max(1, std::min(sm_count() * 8, ceil_div(np, SCH_WARPS)));
+            ba_schur_kernel<<<grid, SCH_WARPS * 32, 0, st>>>(pl.W, nobs, d_cam_idx, pl.pt_ptr, np, pl.V, pl.gp, pl.Dp,
+                                                             lambda, update_D, first_lin, pl.Vinv, pl.bp, pl.S, pl.ld,
+                                                             pl.S + (size_t)pl.npad * pl.ld, pl.gmax, pl.flags + 1);
+            SFM_LAUNCH_CHECK();
+        }
+        if ((rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st)) != SFM_OK) return rc;
+        const int nxt = cur ^ 1;
+        ba_update_cams_kernel<<<1, 256, 0, st>>>(pl.cam[cur], pl.dc, pl.gc, pl.Dc, n, pl.cam[nxt], pl.updpart);
+        SFM_LAUNCH_CHECK();
+        ba_point_rhs_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(pl.W, nobs, d_cam_idx, d_pt_idx, pl.pt_ptr, pl.dc, pl.tp);
+        SFM_LAUNCH_CHECK();
+        ba_update_points_kernel<<<pl.grid_pts, 256, 0, st>>>(pl.pts[cur], pl.Vinv, pl.bp, pl.tp, pl.gp, pl.Dp, np,
+                                                             pl.pts[nxt], pl.updpart);
+        SFM_LAUNCH_CHECK();
+        if ((rc = launch_cam_linearise(pl, K, pl.cam[nxt], pl.camlin[nxt], st)) != SFM_OK) return rc;
+        if ((rc = launch_cost(pl, pl.camlin[nxt], pl.pts[nxt], obs, d_cam_idx, d_pt_idx, nullptr, st)) != SFM_OK) return rc;
+        ba_reduce_scalars_kernel<<<1, 256, 0, st>>>(pl.costpart, pl.grid_obs, pl.updpart, pl.grid_pts + 1, pl.gmax,
+                                                    pl.flags + 1, pl.flags + 2, pl.scal);
+        SFM_LAUNCH_CHECK();
+        SFM_CUDA_TRY(cudaMemcpyAsync(h_scal, pl.scal, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        SFM_CUDA_TRY(cudaStreamSynchronize(st));
+        ++trials;
+        const double cost_new = h_scal[0], sg = h_scal[1], Ds2 = h_scal[2], Dx2n = h_scal[3], Dx2c = h_scal[4];
+        const double gmax = h_scal[5];
+        const int fail = (int)h_scal[6];
+        const double fnorm2 = 2.0 * cost;
+        if (update_D) {
+            // MINPACK gtol test (lmder, top of the outer loop): max_j |J_j^T f| / (|J_j| |f|)
+            double gnorm = fnorm2 > 0.0 ? gmax / sqrt(fnorm2) : 0.0;
+            h_result->gnorm = gnorm;
+            if (gnorm <= o.gtol) { status = 1; break; }
+        }
+        update_D = 0;
+        bool solve_ok = fail == 0 && cost_new == cost_new && Ds2 == Ds2 && sg == sg;
+        if (fail & 4) ++chol_fail;
+        double actred = -1.0, prered = 0.0, ratio = 0.0;
+        if (solve_ok) {
+            if (cost_new <= 1.7e308 && 0.01 * cost_new < cost) actred = 1.0 - cost_new / cost;
+            prered = (sg + lambda * Ds2) / fnorm2;
+            ratio = prered > 0.0 ? actred / prered : 0.0;
+        }
+        const bool accept = solve_ok && ratio >= 1e-4;
+        if (o.verbose)
+            fprintf(stderr, "[sfm_ba] lin %d trial %d lambda %.3e cost %.12g -> %.12g ratio %.4f |Ds| %.3e fail %d %s\n",
+                    h_result->n_linearisations, trials, lambda, cost, cost_new, ratio, sqrt(Ds2 > 0 ? Ds2 : 0), fail,
+                    accept ? "accept" : "reject");
+        if (accept) {
+            cur = nxt;
+            cost = cost_new;
+            xnorm = sqrt(Dx2n);
+            double t = 2.0 * ratio - 1.0;
+            lambda *= fmax(1.0 / 3.0, 1.0 - t * t * t);
+            nu = 2.0;
+        } else {
+            xnorm = sqrt(Dx2c);
+            lambda *= nu;
+            nu *= 2.0;
+        }
+        if (lambda < 1e-20) lambda = 1e-20;
+        if (solve_ok) {
+            bool f = fabs(actred) <= o.ftol && prered <= o.ftol && 0.5 * ratio <= 1.0;
+            bool x = sqrt(Ds2) <= o.xtol * xnorm;
+            if (f && x) status = 4; else if (f) status = 2; else if (x) status = 3;
+        }
+        if (status == -2 && (trials >= o.max_trials || lambda > 1e30)) status = 0;
+        if (status != -2) break;
+        if (accept) {
+            first_lin = 0;
+            update_D = 1;
+            if ((rc = linearise(0)) != SFM_OK) return rc;
+            h_result->n_linearisations += 1;
+        }
+    }
+    SFM_CUDA_TRY(cudaMemcpyAsync(d_cam, pl.cam[cur], sizeof(double) * 6 * nc, cudaMemcpyDeviceToDevice, st));
+    SFM_CUDA_TRY(cudaMemcpyAsync(d_pts, pl.pts[cur], sizeof(double) * 3 * (size_t)np, cudaMemcpyDeviceToDevice, st));
+    SFM_CUDA_TRY(cudaStreamSynchronize(st));
+    h_result->cost = cost;
+    h_result->status = status;
+    h_result->n_trials = trials;
+    h_result->n_chol_fail = chol_fail;
+    h_result->lambda = lambda;
+    return SFM_OK;
+}
