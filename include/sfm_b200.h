@@ -189,6 +189,17 @@ size_t sfm_chol_solve_workspace_bytes(int32_t n);
 int sfm_chol_solve(const double *d_S, const double *d_g, int32_t n, double *d_x, int32_t *d_fail,
                    void *d_ws, size_t ws_bytes, void *stream);
 
+/* Same solve with a per-phase time profile accumulated into d_phase_ns[6] (device, caller-zeroed;
+ * nanoseconds seen by CTA 0: diagonal factor, panel solve, barrier 1, trailing update, barrier 2,
+ * back substitution). Diagnostic entry point used by tools/chol_probe.py. */
+int sfm_chol_solve_profiled(const double *d_S, const double *d_g, int32_t n, double *d_x,
+                            int32_t *d_fail, void *d_ws, size_t ws_bytes, uint64_t *d_phase_ns,
+                            void *stream);
+
+/* Diagnostic: SM cycles of the 48 x 48 diagonal-block factor alone (d_out8[6] column sweep,
+ * [7] whole factor, accumulated; variant must be 0). tools/diag_bench.py. */
+int sfm_chol_diag_bench(const double *d_A48, int32_t variant, uint64_t *d_out8, void *stream);
+
 /* @@MORE@@ (further sections are appended above this marker as the path widens) */
 
 #ifdef __cplusplus

@@ -37,7 +37,7 @@
 namespace sfm {
 
 int chol_solve_launch(double *A, size_t ld, int npad, double *d_Linv, double *d_x, int *d_fail,
-                      cudaStream_t st);
+                      cudaStream_t st, unsigned long long *d_prof);
 constexpr int BA_NB = 48;                 // == CH_NB in chol.cu
 constexpr int BA_CHUNK = 2048;            // observations per camera-pass CTA
 constexpr size_t BA_SMEM_CAM_LIMIT = 200 * 1024;
@@ -892,7 +892,7 @@ extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, c
                                                              pl.S + (size_t)pl.npad * pl.ld, pl.gmax, pl.flags + 1);
             SFM_LAUNCH_CHECK();
         }
-        if ((rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st)) != SFM_OK) return rc;
+        if ((rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st, nullptr)) != SFM_OK) return rc;
         const int nxt = cur ^ 1;
         ba_update_cams_kernel<<<1, 256, 0, st>>>(pl.cam[cur], pl.dc, pl.gc, pl.Dc, n, pl.cam[nxt], pl.updpart);
         SFM_LAUNCH_CHECK();

@@ -20,22 +20,26 @@
 //   phase 2  trailing update A_ij -= L_ik L_jk^T over the lower-triangle tiles, round-robin.
 #include "sfm_common.cuh"
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 namespace cg = cooperative_groups;
 
 namespace sfm {
 
 constexpr int CH_NB = 48;          // panel width: a multiple of 6 (camera blocks) and of 8
-constexpr int CH_LDS = CH_NB + 1;  // padded shared-memory row (conflict-free column access)
+constexpr int CH_LDS = CH_NB + 4;  // padded shared-memory row: stride 52 = 4 mod 16 keeps the 8 x 4 DMMA
+                                   // fragment reads (row = lane>>2, col = lane&3) conflict-free per half-warp
 constexpr int CH_THREADS = 256;
+constexpr int CH_SUPER_MIN = 20;   // trailing blocks from which phase 2 uses 96 x 96 super-tiles
+constexpr int CH_SINGLE_BACK = 16;  // up to this many panels the back substitution runs in one CTA
 
 struct CholSmem {
-    double L[CH_NB * CH_LDS];      // diagonal block / left operand
-    double B[CH_NB * CH_LDS];      // inverse of the diagonal factor / right operand
-    double C[CH_NB * CH_LDS];      // tile being solved or updated
+    // phase 1 / small phase 2: three NB x NB block views L | B | C; large phase 2: panel stages
+    double buf[2 * 2 * 2 * CH_NB * CH_LDS];   // two stages of two 96 x 48 panels
     double x[CH_NB];
     int fail;
 };
+static_assert(2 * 2 * 2 * CH_NB * CH_LDS >= 3 * CH_NB * CH_LDS, "block views must fit");
 
 // load an NB x NB block (rows r0.., cols c0..) of the row-major matrix into padded smem
 __device__ __forceinline__ void load_block(double *s, const double *A, size_t ld, int r0, int c0) {
@@ -51,52 +55,113 @@ __device__ __forceinline__ void store_block(const double *s, double *A, size_t l
     }
 }
 
-// In-place Cholesky of the NB x NB block in sm.L (lower), then sm.B = L^-1 (lower).
-// All threads of the CTA take part. Sets sm.fail on a non-positive pivot.
-__device__ void factor_diag_block(CholSmem &sm) {
-    double *L = sm.L;
-    for (int j = 0; j < CH_NB; ++j) {
-        __syncthreads();
-        double d = L[j * CH_LDS + j];
-        bool bad = !(d > 0.0) || !(d < 1.7e308);
-        double piv = bad ? 1.0 : sqrt(d);
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            L[j * CH_LDS + j] = piv;
-            if (bad) sm.fail = 1;
+// 1/sqrt(d) to full double precision: MUFU seed + two Newton steps (the DP sqrt and divide
+// sequences are several hundred cycles of dependent latency on the critical path of every panel).
+__device__ __forceinline__ double rsqrt_full(double d) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+    double h = 0.5 * d;
+    y = y * fma(-h * y, y, 1.5);
+    y = y * fma(-h * y, y, 1.5);
+    return y;
+}
+
+// Cholesky factor L (first block view of sm.buf, lower, strict upper part zero) and L^-1 (second
+// view) of the NB x NB diagonal block at Ablk (row-major, leading dimension ld, lower triangle
+// read). Right-looking sweep with the block held in REGISTERS: thread (ty, tx) of the 16 x 16
+// layout owns the 3 x 3 entries (ty + 16a, tx + 16b) of A and of M (an identity that receives
+// the same eliminations and so becomes L^-1). Per column j: the unscaled column j of A and row j
+// of M were published to shared memory by their owners at the end of the previous step
+// (double-buffered, so ONE barrier per column); every thread derives 1/sqrt(d) itself, applies
+//     A[i][m] -= a_ij a_mj / d,   M[i][c] -= a_ij m_jc / d
+// to its 3 x 3 tiles without any predicate (entries that are already final or dead just collect
+// garbage that nothing reads), and the finished column of L / row of L^-1 are written out from the
+// published values. ~55 instructions per thread and column; the dependent chain is
+// barrier -> LDS -> rsqrt -> 2 DMUL -> DFMA -> STS (measured on B200: tools/ubench/lat.cu).
+// Sets sm.fail on a non-positive pivot.
+__device__ void factor_diag_block(CholSmem &sm, const double *Ablk, size_t ld, unsigned long long *prof = nullptr) {
+    const long long c0 = clock64();
+    double *Lout = sm.buf, *Xout = sm.buf + CH_NB * CH_LDS;
+    double *pub = sm.buf + 2 * CH_NB * CH_LDS;    // [2][2][NB]: parity x {column of A, row of M}
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    double A[3][3], M[3][3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+            const int r = ty + 16 * a, c = tx + 16 * b;
+            A[a][b] = (c <= r) ? Ablk[(size_t)r * ld + c] : 0.0;
+            M[a][b] = (c == r) ? 1.0 : 0.0;
         }
-        double inv = 1.0 / piv;
-        for (int i = j + 1 + threadIdx.x; i < CH_NB; i += CH_THREADS) L[i * CH_LDS + j] *= inv;
-        __syncthreads();
-        // trailing rank-1 update of the lower triangle: (i, m) with j < m <= i
-        const int rem = CH_NB - 1 - j;
-        for (int e = threadIdx.x; e < rem * rem; e += CH_THREADS) {
-            int a = e / rem, b = e - a * rem;
-            if (b <= a) {
-                int i = j + 1 + a, m = j + 1 + b;
-                L[i * CH_LDS + m] -= L[i * CH_LDS + j] * L[m * CH_LDS + j];
-            }
-        }
-    }
-    __syncthreads();
-    // zero the strict upper part so that products with the block need no masking
     for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
         int r = e / CH_NB, c = e - r * CH_NB;
-        if (c > r) L[r * CH_LDS + c] = 0.0;
-        sm.B[r * CH_LDS + c] = 0.0;
+        Lout[r * CH_LDS + c] = 0.0;
+        Xout[r * CH_LDS + c] = 0.0;
+    }
+    // publish column 0 of A and row 0 of M
+    if (tx == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) pub[ty + 16 * a] = A[a][0];
+    }
+    if (ty == 0) {
+#pragma unroll
+        for (int b = 0; b < 3; ++b) pub[CH_NB + tx + 16 * b] = M[0][b];
     }
     __syncthreads();
-    // B = L^-1: column c by forward substitution, one thread per column
-    if (threadIdx.x < CH_NB) {
-        const int c = threadIdx.x;
-        sm.B[c * CH_LDS + c] = 1.0 / L[c * CH_LDS + c];
-        for (int i = c + 1; i < CH_NB; ++i) {
-            double s = 0.0;
-            for (int m = c; m < i; ++m) s += L[i * CH_LDS + m] * sm.B[m * CH_LDS + c];
-            sm.B[i * CH_LDS + c] = -s / L[i * CH_LDS + i];
+    const long long c1 = clock64();
+    for (int j = 0; j < CH_NB; ++j) {
+        const double *colA = pub + (j & 1) * 2 * CH_NB, *rowM = colA + CH_NB;
+        const double d = colA[j];
+        const bool bad = !(d > 0.0) || !(d < 1.7e308);
+        const double inv = bad ? 1.0 : rsqrt_full(d);
+        const double inv2 = inv * inv;
+        double xi[3], ym[3], mj[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) xi[a] = colA[ty + 16 * a];
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+            ym[b] = colA[tx + 16 * b];
+            mj[b] = rowM[tx + 16 * b];
         }
+        // finished column j of L (rows >= j) and row j of L^-1 (columns <= j)
+        if (tx == (j & 15)) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a)
+                if (ty + 16 * a >= j) Lout[(ty + 16 * a) * CH_LDS + j] = xi[a] * inv;
+        }
+        if (ty == (j & 15)) {
+#pragma unroll
+            for (int b = 0; b < 3; ++b)
+                if (tx + 16 * b <= j) Xout[j * CH_LDS + tx + 16 * b] = mj[b] * inv;
+        }
+        if (threadIdx.x == 0 && bad) sm.fail = 1;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const double xs = xi[a] * inv2;
+#pragma unroll
+            for (int b = 0; b < 3; ++b) {
+                A[a][b] = fma(-xs, ym[b], A[a][b]);
+                M[a][b] = fma(-xs, mj[b], M[a][b]);
+            }
+        }
+        // publish column j+1 of A and row j+1 of M into the other buffer
+        const int jn = j + 1, bn = jn >> 4;
+        double *colN = pub + (jn & 1) * 2 * CH_NB, *rowN = colN + CH_NB;
+        if (tx == (jn & 15)) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) colN[ty + 16 * a] = bn == 0 ? A[a][0] : (bn == 1 ? A[a][1] : A[a][2]);
+        }
+        if (ty == (jn & 15)) {
+#pragma unroll
+            for (int b = 0; b < 3; ++b) rowN[tx + 16 * b] = bn == 0 ? M[0][b] : (bn == 1 ? M[1][b] : M[2][b]);
+        }
+        __syncthreads();
     }
-    __syncthreads();
+    const long long c2 = clock64();
+    if (prof && threadIdx.x == 0) {          // diagnostic: SM cycles of the column sweep / whole factor
+        prof[6] += (unsigned long long)(c2 - c1);
+        prof[7] += (unsigned long long)(clock64() - c0);
+    }
 }
 
 // C(48x48) = or -= X * Y^T with X, Y, C in padded smem; thread (ty, tx) of a 16 x 16 layout owns
@@ -109,8 +174,13 @@ __device__ __forceinline__ void block_xyT(const double *X, const double *Y, doub
     for (int a = 0; a < 3; ++a)
 #pragma unroll
         for (int b = 0; b < 3; ++b) acc[a][b] = 0.0;
+    // each group of four lanes walks the reduction index rotated by one more column: with the row
+    // stride of 52 (= 4 mod 16 banks) this makes the 16 row reads of a half-warp conflict-free
+    const int skew = tx >> 2;
 #pragma unroll 4
-    for (int m = 0; m < CH_NB; ++m) {
+    for (int m0 = 0; m0 < CH_NB; ++m0) {
+        int m = m0 + skew;
+        m = m >= CH_NB ? m - CH_NB : m;
         double xv[3], yv[3];
 #pragma unroll
         for (int a = 0; a < 3; ++a) xv[a] = X[(ty + 16 * a) * CH_LDS + m];
@@ -130,50 +200,280 @@ __device__ __forceinline__ void block_xyT(const double *X, const double *Y, doub
         }
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// ---- phase-2 super-tile: a 96 x 96 block of the trailing matrix (2 x 2 panel blocks) per CTA ----
+// C -= P_I P_J^T with P_I, P_J the 96 x 48 slices of panel k. The panels of the CTA's NEXT tile
+// stream into the other shared-memory stage with cp.async while the current tile is computed;
+// the 6 x 6 accumulators per thread start from C (read straight from global memory before the
+// wait) and go straight back. Rows >= row_lim (beyond the right-hand-side block-row), columns >=
+// col_lim (beyond the matrix) and rows / columns < lo (the panel itself, when the trailing matrix
+// starts on an odd block) are masked.
+constexpr int CH_ST = 2 * CH_NB;               // 96
+constexpr int CH_PANEL = CH_ST * CH_LDS;       // doubles per staged 96 x 48 panel
+
+__device__ __forceinline__ void cp_async_8(double *smem_dst, const double *gmem_src) {
+    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ void issue_panel96(double *s, const double *A, size_t ld, int r0, int c0, int row_lim) {
+    for (int e = threadIdx.x; e < CH_ST * CH_NB; e += CH_THREADS) {
+        int r = e / CH_NB, c = e - r * CH_NB;
+        if (r0 + r < row_lim) cp_async_8(&s[r * CH_LDS + c], &A[(size_t)(r0 + r) * ld + c0 + c]);
+        else s[r * CH_LDS + c] = 0.0;
+    }
+}
+
+struct SuperTiles {
+    int b0, nJ, tri, ntiles;
+    __device__ __forceinline__ void init(int k, int nb) {
+        b0 = (k + 1) >> 1;                       // first super-row/col (may start one block early)
+        const int nI = ((nb + 2) >> 1) - b0;     // super-rows covering block-rows .. nb (RHS)
+        nJ = ((nb + 1) >> 1) - b0;               // super-cols covering block-cols .. nb-1
+        tri = nJ * (nJ + 1) / 2;
+        ntiles = tri + (nI - nJ) * nJ;
+    }
+    __device__ __forceinline__ void decode(int t, int &I, int &J) const {
+        int Ip, Jp;
+        if (t < tri) {
+            Ip = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
+            while ((Ip + 1) * (Ip + 2) / 2 <= t) ++Ip;
+            while (Ip * (Ip + 1) / 2 > t) --Ip;
+            Jp = t - Ip * (Ip + 1) / 2;
+        } else {
+            Ip = nJ + (t - tri) / nJ;
+            Jp = (t - tri) - (Ip - nJ) * nJ;
+        }
+        I = b0 + Ip;
+        J = b0 + Jp;
+    }
+};
+
+// D(8x8) = A(8x4) B(4x8) + C on the FP64 tensor path (DMMA). Fragments: a = A[lane>>2][lane&3],
+// b = B[lane&3][lane>>2], c/d = C[lane>>2][2*(lane&3) + {0,1}].
+__device__ __forceinline__ void dmma_884(double &d0, double &d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+// Tile t of a phase-2 step belongs to: tile 0 (holds the next diagonal block) -> CTA 0, which then
+// factors that block; every other tile round-robin over CTAs 1 .. G-1.
+__device__ __forceinline__ int st_first_tile(int cta, int G) { return (G == 1 || cta == 0) ? 0 : cta; }
+__device__ __forceinline__ int st_next_tile(int t, int cta, int G) {
+    if (G == 1) return t + 1;
+    if (cta == 0) return 0x3fffffff;
+    return t + (G - 1);
+}
+
+template <bool DMMA, class FactorFn>
+__device__ void supertile_phase(CholSmem &sm, double *A, size_t ld, int k, int nb, int cta, int G,
+                                FactorFn &factor_next) {
+    double *buf = sm.buf;
+    SuperTiles st;
+    st.init(k, nb);
+    const int kcol = k * CH_NB, lo = (k + 1) * CH_NB, row_lim = (nb + 1) * CH_NB, col_lim = nb * CH_NB;
+    int t = st_first_tile(cta, G), I = 0, J = 0, stage = 0;
+    __syncthreads();                              // the phase-1 views of buf are dead from here on
+    if (t < st.ntiles) {
+        st.decode(t, I, J);
+        issue_panel96(buf, A, ld, I * CH_ST, kcol, row_lim);
+        if (I != J) issue_panel96(buf + CH_PANEL, A, ld, J * CH_ST, kcol, row_lim);
+    }
+    cp_async_commit();
+    while (t < st.ntiles) {
+        const int tn = st_next_tile(t, cta, G);
+        int In = 0, Jn = 0;
+        if (tn < st.ntiles) {
+            st.decode(tn, In, Jn);
+            double *nxt = buf + (stage ^ 1) * 2 * CH_PANEL;
+            issue_panel96(nxt, A, ld, In * CH_ST, kcol, row_lim);
+            if (In != Jn) issue_panel96(nxt + CH_PANEL, A, ld, Jn * CH_ST, kcol, row_lim);
+        }
+        cp_async_commit();
+        const double *sI = buf + stage * 2 * CH_PANEL;
+        const double *sJ = (I != J) ? sI + CH_PANEL : sI;
+        if (DMMA) {
+            // warp (wr, wc) of a 2 x 4 grid owns rows wr*48.., cols wc*24..: 6 x 3 DMMA tiles
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+            const int wr = warp >> 2, wc = warp & 3, g = lane >> 2, q = lane & 3;
+            const int r0 = I * CH_ST + wr * 48 + g, c0 = J * CH_ST + wc * 24 + 2 * q;
+            double acc[6][3][2];
+#pragma unroll
+            for (int a = 0; a < 6; ++a) {
+                const int r = r0 + 8 * a;
+#pragma unroll
+                for (int b = 0; b < 3; ++b) {
+                    const int c = c0 + 8 * b;       // c even, col_lim and lo even: the pair is in or out together
+                    if (r < row_lim && r >= lo && c < col_lim && c >= lo) {
+                        const double2 v = *reinterpret_cast<const double2 *>(&A[(size_t)r * ld + c]);
+                        acc[a][b][0] = v.x; acc[a][b][1] = v.y;
+                    } else {
+                        acc[a][b][0] = 0.0; acc[a][b][1] = 0.0;
+                    }
+                }
+            }
+            cp_async_wait<1>();                   // everything but the group just committed has landed
+            __syncthreads();
+            const double *pa = sI + (wr * 48 + g) * CH_LDS + q;
+            const double *pb = sJ + (wc * 24 + g) * CH_LDS + q;
+#pragma unroll 3
+            for (int k4 = 0; k4 < CH_NB; k4 += 4) {
+                double af[6], bf[3];
+#pragma unroll
+                for (int a = 0; a < 6; ++a) af[a] = -pa[a * 8 * CH_LDS + k4];
+#pragma unroll
+                for (int b = 0; b < 3; ++b) bf[b] = pb[b * 8 * CH_LDS + k4];
+#pragma unroll
+                for (int a = 0; a < 6; ++a)
+#pragma unroll
+                    for (int b = 0; b < 3; ++b) dmma_884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+            }
+#pragma unroll
+            for (int a = 0; a < 6; ++a) {
+                const int r = r0 + 8 * a;
+                if (r >= row_lim || r < lo) continue;
+#pragma unroll
+                for (int b = 0; b < 3; ++b) {
+                    const int c = c0 + 8 * b;
+                    if (c < col_lim && c >= lo)
+                        *reinterpret_cast<double2 *>(&A[(size_t)r * ld + c]) = make_double2(acc[a][b][0], acc[a][b][1]);
+                }
+            }
+        } else {
+            const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+            double acc[6][6];
+#pragma unroll
+            for (int a = 0; a < 6; ++a) {
+                const int r = I * CH_ST + ty + 16 * a;
+#pragma unroll
+                for (int b = 0; b < 6; ++b) {
+                    const int c = J * CH_ST + tx + 16 * b;
+                    acc[a][b] = (r < row_lim && r >= lo && c < col_lim && c >= lo) ? A[(size_t)r * ld + c] : 0.0;
+                }
+            }
+            cp_async_wait<1>();
+            __syncthreads();
+            const int skew = tx >> 2;
+#pragma unroll 2
+            for (int m0 = 0; m0 < CH_NB; ++m0) {
+                int m = m0 + skew;
+                m = m >= CH_NB ? m - CH_NB : m;
+                double xv[6], yv[6];
+#pragma unroll
+                for (int a = 0; a < 6; ++a) xv[a] = -sI[(ty + 16 * a) * CH_LDS + m];
+#pragma unroll
+                for (int b = 0; b < 6; ++b) yv[b] = sJ[(tx + 16 * b) * CH_LDS + m];
+#pragma unroll
+                for (int a = 0; a < 6; ++a)
+#pragma unroll
+                    for (int b = 0; b < 6; ++b) acc[a][b] = fma(xv[a], yv[b], acc[a][b]);
+            }
+#pragma unroll
+            for (int a = 0; a < 6; ++a) {
+                const int r = I * CH_ST + ty + 16 * a;
+                if (r >= row_lim || r < lo) continue;
+#pragma unroll
+                for (int b = 0; b < 6; ++b) {
+                    const int c = J * CH_ST + tx + 16 * b;
+                    if (c < col_lim && c >= lo) A[(size_t)r * ld + c] = acc[a][b];
+                }
+            }
+        }
+        __syncthreads();                          // this stage may be refilled by the next iteration's loads
+        if (t == 0) factor_next(k + 1);           // look-ahead: tile 0 holds the next diagonal block; its
+                                                  // factor works in this (now free) stage's first 3 views
+        stage ^= 1;
+        t = tn;
+        I = In;
+        J = Jn;
+    }
+    cp_async_wait<0>();
+}
+
 // nb = npad / NB diagonal blocks; block-row nb is the right-hand side. x_out [npad].
 // Linv_ws [nb, NB*NB]: inverses of the diagonal factors (for the backward substitution).
+template <bool DMMA>
 __global__ void __launch_bounds__(CH_THREADS)
 chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict__ Linv_ws,
-                  double *__restrict__ x_out, int *__restrict__ fail_flag) {
+                  double *__restrict__ x_out, int *__restrict__ fail_flag,
+                  unsigned long long *__restrict__ prof) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     CholSmem &sm = *reinterpret_cast<CholSmem *>(smem_raw);
     cg::grid_group grid = cg::this_grid();
     const int G = gridDim.x, cta = blockIdx.x;
     if (threadIdx.x == 0) sm.fail = 0;
     __syncthreads();
+    double *const sL = sm.buf, *const sB = sm.buf + CH_NB * CH_LDS, *const sC = sm.buf + 2 * CH_NB * CH_LDS;
+    // optional phase profile (CTA 0, thread 0; ns): [0] diag factor [1] panel solve [2] barrier 1
+    // [3] trailing update [4] barrier 2 [5] back substitution
+    const bool profiling = prof != nullptr && cta == 0 && threadIdx.x == 0;
+    unsigned long long t_prev = profiling ? globaltimer_ns() : 0ull;
+#define CH_TICK(slot)                                              \
+    do {                                                           \
+        if (profiling) {                                           \
+            unsigned long long t_now = globaltimer_ns();           \
+            prof[slot] += t_now - t_prev;                          \
+            t_prev = t_now;                                        \
+        }                                                          \
+    } while (0)
+
+    // Diagonal block kb: factor it, commit L_kb,kb to A and its inverse to Linv_ws (CTA 0 only).
+    auto factor_and_commit = [&](int kb) {
+        __syncthreads();
+        factor_diag_block(sm, A + (size_t)kb * CH_NB * ld + kb * CH_NB, ld, prof);
+        store_block(sL, A, ld, kb * CH_NB, kb * CH_NB);
+        for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
+            int r = e / CH_NB, c = e - r * CH_NB;
+            Linv_ws[(size_t)kb * CH_NB * CH_NB + e] = sB[r * CH_LDS + c];
+        }
+        if (threadIdx.x == 0 && sm.fail) *fail_flag = 1;
+        __syncthreads();
+    };
+    if (cta == 0) factor_and_commit(0);
+    CH_TICK(0);
+    grid.sync();
+    CH_TICK(2);
 
     for (int k = 0; k < nb; ++k) {
-        // ---- phase 1: diagonal factor (redundant per CTA) + panel solve ----
+        // ---- phase 1: panel solve A_ik <- A_ik L_kk^-T with the inverse committed one phase earlier ----
         const int rows_below = nb - k;            // block-rows k+1 .. nb (nb = RHS)
-        if (cta < rows_below || cta == 0) {
-            load_block(sm.L, A, ld, k * CH_NB, k * CH_NB);
-            factor_diag_block(sm);
-            if (cta == 0) {
-                store_block(sm.L, A, ld, k * CH_NB, k * CH_NB);
-                for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
-                    int r = e / CH_NB, c = e - r * CH_NB;
-                    Linv_ws[(size_t)k * CH_NB * CH_NB + e] = sm.B[r * CH_LDS + c];
-                }
-                if (threadIdx.x == 0 && sm.fail) *fail_flag = 1;
+        if (cta < rows_below) {
+            for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
+                int r = e / CH_NB, c = e - r * CH_NB;
+                sB[r * CH_LDS + c] = Linv_ws[(size_t)k * CH_NB * CH_NB + e];
             }
             for (int i = k + 1 + cta; i <= nb; i += G) {
                 __syncthreads();
-                load_block(sm.C, A, ld, i * CH_NB, k * CH_NB);
+                load_block(sC, A, ld, i * CH_NB, k * CH_NB);
                 __syncthreads();
-                // X = A_ik L^-T :  X[r][c] = sum_m A_ik[r][m] Linv[c][m]; result into sm.L? no:
-                // sm.L holds the factor (unused from here on in this step) -> reuse as output
-                block_xyT<0>(sm.C, sm.B, sm.L);
+                // X = A_ik L^-T : X[r][c] = sum_m A_ik[r][m] Linv[c][m]
+                block_xyT<0>(sC, sB, sL);
                 __syncthreads();
-                store_block(sm.L, A, ld, i * CH_NB, k * CH_NB);
+                store_block(sL, A, ld, i * CH_NB, k * CH_NB);
             }
         }
+        CH_TICK(1);
         grid.sync();
-        // ---- phase 2: trailing update over tiles (i, j), k < j <= i <= nb, j < nb ----
+        CH_TICK(2);
+        // ---- phase 2: trailing update over tiles (i, j), k < j <= i <= nb, j < nb. Look-ahead: the CTA
+        // that updates the tile holding the next diagonal block (tile 0 = CTA 0) factors that block
+        // right away, so the factor overlaps the rest of the update instead of heading phase 1. ----
         const int m = nb - 1 - k;                 // remaining diagonal blocks
-        if (m > 0) {
+        if (m >= CH_SUPER_MIN) {
+            // 96 x 96 super-tiles over the trailing block rows k+1 .. nb, aligned to even block indices
+            supertile_phase<DMMA>(sm, A, ld, k, nb, cta, G, factor_and_commit);
+        } else if (m > 0) {
             // tiles: for j' in [0, m): i' in [j', m]  (i' == m is the RHS block-row)
             const int ntiles = m * (m + 1) / 2 + m;
-            for (int t = cta; t < ntiles; t += G) {
+            for (int t = st_first_tile(cta, G); t < ntiles; t = st_next_tile(t, cta, G)) {
                 int ip, jp;
                 if (t < m * (m + 1) / 2) {
                     // lower triangle of an m x m block matrix, row-major enumeration
@@ -187,20 +487,63 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
                 }
                 const int i = k + 1 + ip, j = k + 1 + jp;
                 __syncthreads();
-                load_block(sm.L, A, ld, i * CH_NB, k * CH_NB);
-                load_block(sm.B, A, ld, j * CH_NB, k * CH_NB);
-                load_block(sm.C, A, ld, i * CH_NB, j * CH_NB);
+                load_block(sL, A, ld, i * CH_NB, k * CH_NB);
+                load_block(sB, A, ld, j * CH_NB, k * CH_NB);
+                load_block(sC, A, ld, i * CH_NB, j * CH_NB);
                 __syncthreads();
-                block_xyT<1>(sm.L, sm.B, sm.C);
+                block_xyT<1>(sL, sB, sC);
                 __syncthreads();
-                store_block(sm.C, A, ld, i * CH_NB, j * CH_NB);
+                store_block(sC, A, ld, i * CH_NB, j * CH_NB);
+                if (t == 0) {
+                    CH_TICK(3);
+                    factor_and_commit(k + 1);
+                    CH_TICK(0);
+                }
             }
         }
+        CH_TICK(3);
         grid.sync();
+        CH_TICK(4);
     }
 
     // ---- backward substitution L^T x = y, y = first row of the RHS block-row ----
     const double *yrow = A + (size_t)nb * CH_NB * ld;
+    if (nb <= CH_SINGLE_BACK) {
+        // small systems: one CTA, block barriers only
+        if (cta != 0) return;
+        for (int e = threadIdx.x; e < nb * CH_NB; e += CH_THREADS) x_out[e] = yrow[e];
+        for (int k = nb - 1; k >= 0; --k) {
+            __syncthreads();
+            if (threadIdx.x < CH_NB) sm.x[threadIdx.x] = x_out[k * CH_NB + threadIdx.x];
+            __syncthreads();
+            // x_k = Linv_kk^T y_k: thread (c, part) sums a quarter of the rows, combined through smem
+            {
+                const double *Li = Linv_ws + (size_t)k * CH_NB * CH_NB;
+                const int c = threadIdx.x & 63, part = threadIdx.x >> 6;
+                double s = 0.0;
+                if (c < CH_NB)
+#pragma unroll 4
+                    for (int r = part * 12; r < part * 12 + 12; ++r)
+                        if (r >= c) s += Li[r * CH_NB + c] * sm.x[r];
+                sC[part * 64 + c] = s;
+            }
+            __syncthreads();
+            if (threadIdx.x < CH_NB)
+                sB[threadIdx.x] = sC[threadIdx.x] + sC[64 + threadIdx.x] + sC[128 + threadIdx.x] +
+                                    sC[192 + threadIdx.x];
+            __syncthreads();
+            if (threadIdx.x < CH_NB) x_out[k * CH_NB + threadIdx.x] = sB[threadIdx.x];
+            // y_j -= sum_r L[k*NB + r][j] x_k[r] for all columns j < k*NB
+            for (int j = threadIdx.x; j < k * CH_NB; j += CH_THREADS) {
+                double s = 0.0;
+#pragma unroll 8
+                for (int r = 0; r < CH_NB; ++r) s += A[(size_t)(k * CH_NB + r) * ld + j] * sB[r];
+                x_out[j] -= s;
+            }
+        }
+        CH_TICK(5);
+        return;
+    }
     for (int e = cta * CH_THREADS + threadIdx.x; e < nb * CH_NB; e += G * CH_THREADS) x_out[e] = yrow[e];
     grid.sync();
     for (int k = nb - 1; k >= 0; --k) {
@@ -208,39 +551,69 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
         __syncthreads();
         if (threadIdx.x < CH_NB) sm.x[threadIdx.x] = x_out[k * CH_NB + threadIdx.x];
         __syncthreads();
-        double xk = 0.0;
-        if (threadIdx.x < CH_NB) {
+        {
             const double *Li = Linv_ws + (size_t)k * CH_NB * CH_NB;
-            const int c = threadIdx.x;
-            for (int r = c; r < CH_NB; ++r) xk += Li[r * CH_NB + c] * sm.x[r];
+            const int c = threadIdx.x & 63, part = threadIdx.x >> 6;
+            double s = 0.0;
+            if (c < CH_NB)
+#pragma unroll 4
+                for (int r = part * 12; r < part * 12 + 12; ++r)
+                    if (r >= c) s += Li[r * CH_NB + c] * sm.x[r];
+            sC[part * 64 + c] = s;
         }
         __syncthreads();
-        if (threadIdx.x < CH_NB) sm.x[threadIdx.x] = xk;
+        if (threadIdx.x < CH_NB)
+            sB[threadIdx.x] = sC[threadIdx.x] + sC[64 + threadIdx.x] + sC[128 + threadIdx.x] +
+                                sC[192 + threadIdx.x];
         __syncthreads();
-        // y_b -= L_kb^T x_k for b < k, round-robin over CTAs; CTA (k % G) also commits x_k
+        // y_b -= L_kb^T x_k for b < k: (block, quarter of the rows) pairs round-robin over CTAs would
+        // need atomics; instead each CTA takes whole column blocks, 4 row-quarters per thread group
         for (int b = cta; b < k; b += G) {
-            if (threadIdx.x < CH_NB) {
-                const int c = threadIdx.x;
-                double s = 0.0;
-                for (int r = 0; r < CH_NB; ++r)
-                    s += A[(size_t)(k * CH_NB + r) * ld + b * CH_NB + c] * sm.x[r];
-                x_out[b * CH_NB + c] -= s;
-            }
+            const int c = threadIdx.x & 63, part = threadIdx.x >> 6;
+            double s = 0.0;
+            if (c < CH_NB)
+#pragma unroll 4
+                for (int r = part * 12; r < part * 12 + 12; ++r)
+                    s += A[(size_t)(k * CH_NB + r) * ld + b * CH_NB + c] * sB[r];
+            __syncthreads();
+            sC[part * 64 + c] = s;
+            __syncthreads();
+            if (threadIdx.x < CH_NB)
+                x_out[b * CH_NB + threadIdx.x] -= sC[threadIdx.x] + sC[64 + threadIdx.x] +
+                                                  sC[128 + threadIdx.x] + sC[192 + threadIdx.x];
         }
         grid.sync();
-        if (cta == 0 && threadIdx.x < CH_NB) x_out[k * CH_NB + threadIdx.x] = sm.x[threadIdx.x];
+        if (cta == 0 && threadIdx.x < CH_NB) x_out[k * CH_NB + threadIdx.x] = sB[threadIdx.x];
     }
+    CH_TICK(5);
+#undef CH_TICK
+}
+
+// diagnostic: cycles of the diagonal-block factor alone (one CTA)
+__global__ void __launch_bounds__(CH_THREADS) chol_diag_bench_kernel(const double *A48, unsigned long long *out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    CholSmem &sm = *reinterpret_cast<CholSmem *>(smem_raw);
+    factor_diag_block(sm, A48, CH_NB, out);
 }
 
 static int g_chol_grid = 0;
+static int g_chol_dmma = -1;
+
+static bool chol_use_dmma() {
+    if (g_chol_dmma < 0) {
+        const char *e = getenv("SFM_CHOL_DFMA");          // development switch: plain DFMA trailing update
+        g_chol_dmma = (e && e[0] == '1') ? 0 : 1;
+    }
+    return g_chol_dmma == 1;
+}
 
 int chol_grid_size() {
     if (g_chol_grid) return g_chol_grid;
     int per_sm = 0;
-    if (cudaFuncSetAttribute(chol_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)sizeof(CholSmem)) != cudaSuccess ||
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, chol_solve_kernel, CH_THREADS,
-                                                      sizeof(CholSmem)) != cudaSuccess || per_sm < 1) {
+    const void *fn = chol_use_dmma() ? (const void *)chol_solve_kernel<true> : (const void *)chol_solve_kernel<false>;
+    if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem)) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, CH_THREADS, sizeof(CholSmem)) != cudaSuccess ||
+        per_sm < 1) {
         (void)cudaGetLastError();
         return 0;
     }
@@ -251,17 +624,16 @@ int chol_grid_size() {
 // Enqueue the factor+solve. A: (npad + NB) x ld; d_Linv: nb*NB*NB doubles; d_x: npad doubles;
 // d_fail: int (zeroed by the caller).
 int chol_solve_launch(double *A, size_t ld, int npad, double *d_Linv, double *d_x, int *d_fail,
-                      cudaStream_t st) {
+                      cudaStream_t st, unsigned long long *d_prof) {
     int G = chol_grid_size();
     if (G <= 0) return SFM_E_CUDA;
     int nb = npad / CH_NB;
     // no point in more CTAs than the widest phase can use
-    int need = nb * (nb + 1) / 2 + nb;
-    if (need < 1) need = 1;
+    int need = nb * (nb + 1) / 2 + nb + 1;
     if (G > need) G = need;
-    void *args[] = {&A, &ld, &nb, &d_Linv, &d_x, &d_fail};
-    cudaError_t e = cudaLaunchCooperativeKernel((void *)chol_solve_kernel, dim3(G), dim3(CH_THREADS), args,
-                                                sizeof(CholSmem), st);
+    void *args[] = {&A, &ld, &nb, &d_Linv, &d_x, &d_fail, &d_prof};
+    const void *fn = chol_use_dmma() ? (const void *)chol_solve_kernel<true> : (const void *)chol_solve_kernel<false>;
+    cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(G), dim3(CH_THREADS), args, sizeof(CholSmem), st);
     count_launch();
     if (e != cudaSuccess) {
         record_cuda_error(e, "cudaLaunchCooperativeKernel(chol_solve_kernel)");
@@ -297,8 +669,8 @@ extern "C" size_t sfm_chol_solve_workspace_bytes(int32_t n) {
     return bytes;
 }
 
-extern "C" int sfm_chol_solve(const double *d_S, const double *d_g, int32_t n, double *d_x,
-                              int32_t *d_fail, void *d_ws, size_t ws_bytes, void *stream) {
+static int chol_solve_impl(const double *d_S, const double *d_g, int32_t n, double *d_x, int32_t *d_fail,
+                           void *d_ws, size_t ws_bytes, void *stream, unsigned long long *d_prof) {
     if (!d_S || !d_g || !d_x || !d_fail || !d_ws || n < 1) return SFM_E_INVALID;
     if (ws_bytes < sfm_chol_solve_workspace_bytes(n)) return SFM_E_WORKSPACE;
     cudaStream_t st = as_stream(stream);
@@ -311,9 +683,33 @@ extern "C" int sfm_chol_solve(const double *d_S, const double *d_g, int32_t n, d
     SFM_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), st));
     chol_pack_kernel<<<sm_count() * 4, 256, 0, st>>>(d_S, d_g, n, npad, ld, A);
     SFM_LAUNCH_CHECK();
-    int rc = chol_solve_launch(A, ld, npad, Linv, x, flag, st);
+    int rc = chol_solve_launch(A, ld, npad, Linv, x, flag, st, d_prof);
     if (rc != SFM_OK) return rc;
     SFM_CUDA_TRY(cudaMemcpyAsync(d_x, x, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st));
     SFM_CUDA_TRY(cudaMemcpyAsync(d_fail, flag, sizeof(int), cudaMemcpyDeviceToDevice, st));
+    return SFM_OK;
+}
+
+extern "C" int sfm_chol_solve(const double *d_S, const double *d_g, int32_t n, double *d_x,
+                              int32_t *d_fail, void *d_ws, size_t ws_bytes, void *stream) {
+    return chol_solve_impl(d_S, d_g, n, d_x, d_fail, d_ws, ws_bytes, stream, nullptr);
+}
+
+extern "C" int sfm_chol_solve_profiled(const double *d_S, const double *d_g, int32_t n, double *d_x,
+                                       int32_t *d_fail, void *d_ws, size_t ws_bytes, uint64_t *d_phase_ns,
+                                       void *stream) {
+    if (!d_phase_ns) return SFM_E_INVALID;
+    return chol_solve_impl(d_S, d_g, n, d_x, d_fail, d_ws, ws_bytes, stream,
+                           reinterpret_cast<unsigned long long *>(d_phase_ns));
+}
+
+extern "C" int sfm_chol_diag_bench(const double *d_A48, int32_t variant, uint64_t *d_out8, void *stream) {
+    if (!d_A48 || !d_out8 || variant != 0) return SFM_E_INVALID;
+    cudaStream_t st = as_stream(stream);
+    if (chol_grid_size() <= 0) return SFM_E_CUDA;
+    SFM_CUDA_TRY(cudaFuncSetAttribute(chol_diag_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(CholSmem)));
+    chol_diag_bench_kernel<<<1, CH_THREADS, sizeof(CholSmem), st>>>(d_A48, reinterpret_cast<unsigned long long *>(d_out8));
+    SFM_LAUNCH_CHECK();
     return SFM_OK;
 }

@@ -26,7 +26,7 @@ def _rmse(cost, n_obs):
     return np.sqrt(2.0 * cost / n_obs)
 
 
-@pytest.mark.parametrize("n", [5, 48, 49, 300, 306, 1000])
+@pytest.mark.parametrize("n", [5, 48, 49, 300, 306, 768, 1000, 1105, 2400, 3001])
 def test_chol_solve_matches_lapack(cuda_device, n):
     import torch
     from sfm_b200 import _lib, device
