@@ -254,6 +254,12 @@ def run_ours(args, rank, world):
                "clocks": clocks.summary()}
         if world == 1:
             out["cpu_baseline"] = cpu_baseline_single(sc, samples_all, n_hyp=args.cpu_hyp)
+            if not args.skip_ba:
+                import bench_ba
+                del d_x, d_s_all, d_s, plan
+                out["ba"] = bench_ba.run_single_gpu(args, peaks, peak_src, flush)
+                out["ba"]["cpu_baseline"] = bench_ba.cpu_baseline()
+                out["gpu_launches"] += out["ba"]["gpu_launches"]
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -266,6 +272,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-hyp", type=int, default=6000, help="hypotheses in the 1-core CPU baseline sample")
+    ap.add_argument("--skip-ba", action="store_true", help="F-RANSAC part only")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

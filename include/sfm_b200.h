@@ -150,6 +150,9 @@ typedef struct sfm_ba_options {
     int32_t verbose;     /* 1: one line per trial step on stderr */
     double ftol, xtol, gtol; /* MINPACK / scipy stopping tolerances (reference: scipy default 1e-8) */
     double lambda0;      /* initial damping of (J^T J + lambda D^2); D = Jacobian column norms */
+    int32_t reuse_index; /* 1: d_ws still holds the camera-major index of a previous sfm_ba_solve call
+                            on the SAME d_cam_idx / d_pt_idx contents (skips the index build) */
+    int32_t reserved;
 } sfm_ba_options;
 
 typedef struct sfm_ba_result {
@@ -181,6 +184,14 @@ int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, const int32_
                  const int32_t *d_pt_idx, int32_t n_cams, int32_t n_pts, int32_t n_obs,
                  const double *h_K, const sfm_ba_options *opts, sfm_ba_result *h_result,
                  void *d_ws, size_t ws_bytes, void *stream);
+
+/* One linearisation pass in isolation, for bench.py / ncu (the passes of sfm_ba_solve, same kernels):
+ * which = bit 0 point pass K9p (W, V, g_p, cost partials), bit 1 camera pass K9c (U, g_c), bit 2 cost
+ * pass K8, bit 3 reuse the linearised-camera table of the previous call. Outputs stay in d_ws. */
+int sfm_ba_linearise(const double *d_cam, const double *d_pts, const double *d_obs,
+                     const int32_t *d_cam_idx, const int32_t *d_pt_idx, int32_t n_cams, int32_t n_pts,
+                     int32_t n_obs, const double *h_K, int32_t which, int32_t reuse_index, void *d_ws,
+                     size_t ws_bytes, void *stream);
 
 /* K11 alone: dense SPD solve S x = g by the blocked Cholesky used inside sfm_ba_solve.
  * d_S [n,n] row-major (lower triangle read), d_g [n], d_x [n] out, d_fail[0] = 1 when a pivot

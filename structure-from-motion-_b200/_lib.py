@@ -48,6 +48,8 @@ SIGNATURES = {
                                    c_vp, c_f64p, c_f64p, c_vp, C.c_size_t, c_vp]),
     "sfm_ba_solve": (C.c_int, [c_f64p, c_f64p, c_f64p, c_i32p, c_i32p, C.c_int32, C.c_int32, C.c_int32,
                                c_vp, c_vp, c_vp, c_vp, C.c_size_t, c_vp]),
+    "sfm_ba_linearise": (C.c_int, [c_f64p, c_f64p, c_f64p, c_i32p, c_i32p, C.c_int32, C.c_int32, C.c_int32,
+                                   c_vp, C.c_int32, C.c_int32, c_vp, C.c_size_t, c_vp]),
     "sfm_chol_solve_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "sfm_chol_solve": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_i32p, c_vp, C.c_size_t, c_vp]),
     "sfm_chol_diag_bench": (C.c_int, [c_f64p, C.c_int32, c_vp, c_vp]),
@@ -59,7 +61,8 @@ SIGNATURES = {
 class BAOptions(C.Structure):
     """sfm_ba_options (include/sfm_b200.h)."""
     _fields_ = [("max_trials", C.c_int32), ("verbose", C.c_int32), ("ftol", C.c_double),
-                ("xtol", C.c_double), ("gtol", C.c_double), ("lambda0", C.c_double)]
+                ("xtol", C.c_double), ("gtol", C.c_double), ("lambda0", C.c_double), ("reuse_index", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 class BAResult(C.Structure):

@@ -51,6 +51,7 @@ class BAProblem:
         if self.ws_bytes == 0:
             raise ValueError("empty bundle adjustment problem")
         self.ws = device.empty((self.ws_bytes,), torch.uint8)
+        self._indexed = False          # the workspace holds this problem's camera-major index
 
     def residuals_device(self, d_cam, d_pts, want_r=True):
         """K8: (d_r [n_obs,2] or None, d_cost [1]) at the given parameters."""
@@ -63,6 +64,17 @@ class BAProblem:
         _lib.check(rc, "sfm_ba_residuals")
         return d_r, d_cost
 
+    def linearise_device(self, d_cam, d_pts, which=3, reuse_table=False):
+        """One linearisation pass in isolation (bench / profiling): which = 1 point pass K9p, 2 camera
+        pass K9c, 4 cost pass K8 (bit mask)."""
+        rc = _lib.load().sfm_ba_linearise(
+            device.ptr(d_cam), device.ptr(d_pts), device.ptr(self.d_obs), device.ptr(self.d_cam_idx),
+            device.ptr(self.d_pt_idx), self.n_cams, self.n_pts, self.n_obs, _hptr(self.K),
+            int(which) | (8 if reuse_table else 0), int(self._indexed), device.ptr(self.ws), self.ws_bytes,
+            device.stream())
+        _lib.check(rc, "sfm_ba_linearise")
+        self._indexed = True
+
     def solve_device(self, d_cam, d_pts, max_nfev=BA_MAX_NFEV, tol=REF_TOL, lambda0=1e-4, verbose=False):
         """K8-K12 LM; d_cam [n_cams,6] and d_pts [n_pts,3] are refined in place. Returns a dict."""
         lib = _lib.load()
@@ -71,12 +83,14 @@ class BAProblem:
         opts.max_trials, opts.verbose = int(max_nfev), int(bool(verbose))
         opts.ftol = opts.xtol = opts.gtol = float(tol)
         opts.lambda0 = float(lambda0)
+        opts.reuse_index = int(self._indexed)
         res = _lib.BAResult()
         rc = lib.sfm_ba_solve(
             device.ptr(d_cam), device.ptr(d_pts), device.ptr(self.d_obs), device.ptr(self.d_cam_idx),
             device.ptr(self.d_pt_idx), self.n_cams, self.n_pts, self.n_obs, _hptr(self.K),
             C.addressof(opts), C.addressof(res), device.ptr(self.ws), self.ws_bytes, device.stream())
         _lib.check(rc, "sfm_ba_solve")
+        self._indexed = True
         return dict(cost0=res.cost0, cost=res.cost, gnorm=res.gnorm, lambda_=res.lambda_, status=res.status,
                     n_linearisations=res.n_linearisations, n_trials=res.n_trials, n_chol_fail=res.n_chol_fail)
 

@@ -32,6 +32,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 namespace sfm {
@@ -667,11 +668,11 @@ static void set_obs_kernel_attrs(size_t smem) {
     cudaFuncSetAttribute(ba_cost_kernel<SM, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
-static int launch_point_pass(const BAPlan &pl, const KParam &K, int cur, const double2 *obs,
-                             const int32_t *cam_idx, const int32_t *pt_idx, cudaStream_t st) {
+static int launch_point_pass(const BAPlan &pl, const KParam &K, const double *camlin, const double *pts,
+                             const double2 *obs, const int32_t *cam_idx, const int32_t *pt_idx, cudaStream_t st) {
     SFM_CUDA_TRY(cudaMemsetAsync(pl.V, 0, sizeof(double) * 9 * (size_t)pl.np, st));
     const size_t sm = pl.smem_cams ? pl.cam_smem : 0;
-#define PP_ARGS K, pl.camlin[cur], pl.nc, pl.pts[cur], obs, cam_idx, pt_idx, pl.pt_ptr, pl.nobs, pl.W, pl.V, pl.gp, pl.costpart
+#define PP_ARGS K, camlin, pl.nc, pts, obs, cam_idx, pt_idx, pl.pt_ptr, pl.nobs, pl.W, pl.V, pl.gp, pl.costpart
     if (pl.smem_cams) {
         if (pl.obs_threads == 512) ba_point_pass_kernel<true, 512, 1><<<pl.grid_obs, 512, sm, st>>>(PP_ARGS);
         else ba_point_pass_kernel<true, 256, 2><<<pl.grid_obs, 256, sm, st>>>(PP_ARGS);
@@ -766,6 +767,7 @@ extern "C" void sfm_ba_default_options(sfm_ba_options *o) {
     o->verbose = 0;
     o->ftol = o->xtol = o->gtol = 1e-8;   // scipy least_squares defaults
     o->lambda0 = 1e-4;
+    o->reuse_index = 0;
 }
 
 extern "C" size_t sfm_ba_workspace_bytes(int32_t n_cams, int32_t n_pts, int32_t n_obs) {
@@ -775,6 +777,40 @@ extern "C" size_t sfm_ba_workspace_bytes(int32_t n_cams, int32_t n_pts, int32_t 
 }
 
 static bool g_attrs_set = false;
+
+struct PlanKey {
+    const void *ws, *cam_idx;
+    int nc, np, nobs, nchunks;
+};
+static std::mutex g_plan_mu;
+static std::vector<PlanKey> g_plans;
+
+
+// Index structures: built once per (workspace, problem shape) when the caller vouches for
+// unchanged indices (reuse), else on every call.
+static int ba_acquire_index(BAPlan &pl, bool reuse, const void *d_ws, const double2 *obs, const int32_t *d_cam_idx,
+                            const int32_t *d_pt_idx, int n_cams, int n_pts, int n_obs, cudaStream_t st) {
+    if (reuse) {
+        std::lock_guard<std::mutex> g(g_plan_mu);
+        for (const PlanKey &pk : g_plans)
+            if (pk.ws == d_ws && pk.nc == n_cams && pk.np == n_pts && pk.nobs == n_obs && pk.cam_idx == d_cam_idx) {
+                pl.nchunks = pk.nchunks;
+                return SFM_OK;
+            }
+    }
+    int rc = ba_build_index(pl, obs, d_cam_idx, d_pt_idx, st);
+    if (rc != SFM_OK) return rc;
+    std::lock_guard<std::mutex> g(g_plan_mu);
+    PlanKey pk{d_ws, d_cam_idx, n_cams, n_pts, n_obs, pl.nchunks};
+    bool found = false;
+    for (PlanKey &q : g_plans)
+        if (q.ws == d_ws) { q = pk; found = true; }
+    if (!found) {
+        if (g_plans.size() >= 16) g_plans.erase(g_plans.begin());
+        g_plans.push_back(pk);
+    }
+    return SFM_OK;
+}
 
 static int ba_prepare(BAPlan &pl, void *d_ws, size_t ws_bytes, int32_t n_cams, int32_t n_pts, int32_t n_obs) {
     if (n_cams < 1 || n_pts < 1 || n_obs < 1 || !d_ws) return SFM_E_INVALID;
@@ -836,19 +872,19 @@ extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, c
     memset(h_result, 0, sizeof(*h_result));
     h_result->status = -1;
 
-    if ((rc = ba_build_index(pl, obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return rc;
+    if ((rc = ba_acquire_index(pl, o.reuse_index != 0, d_ws, obs, d_cam_idx, d_pt_idx, n_cams, n_pts, n_obs, st)) != SFM_OK) return rc;
     const int nc = pl.nc, np = pl.np, nobs = pl.nobs, n = 6 * nc;
     SFM_CUDA_TRY(cudaMemcpyAsync(pl.cam[0], d_cam, sizeof(double) * 6 * nc, cudaMemcpyDeviceToDevice, st));
     SFM_CUDA_TRY(cudaMemcpyAsync(pl.pts[0], d_pts, sizeof(double) * 3 * (size_t)np, cudaMemcpyDeviceToDevice, st));
     int cur = 0;
-    double *h_scal = nullptr;
-    SFM_CUDA_TRY(cudaMallocHost(&h_scal, 16 * sizeof(double)));
-    struct Pinned { double *p; ~Pinned() { cudaFreeHost(p); } } pinned{h_scal};
+    // pinned landing zone for the per-trial scalars: one per host thread, allocated once
+    static thread_local double *h_scal = nullptr;
+    if (!h_scal) SFM_CUDA_TRY(cudaMallocHost(&h_scal, 16 * sizeof(double)));
 
     auto linearise = [&](int first) -> int {
         int r;
         SFM_CUDA_TRY(cudaMemsetAsync(pl.gmax, 0, 8, st));
-        if ((r = launch_point_pass(pl, K, cur, obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return r;
+        if ((r = launch_point_pass(pl, K, pl.camlin[cur], pl.pts[cur], obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return r;
         if (pl.nchunks) {
             ba_camera_pass_kernel<<<pl.nchunks, 256, 0, st>>>(K, pl.camlin[cur], pl.pts[cur], pl.obs_c, pl.pt_c,
                                                               pl.chunk_cam, pl.chunk_beg, pl.chunk_end, pl.Upart);
@@ -968,5 +1004,43 @@ extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, c
     h_result->n_trials = trials;
     h_result->n_chol_fail = chol_fail;
     h_result->lambda = lambda;
+    return SFM_OK;
+}
+
+// One linearisation pass in isolation (bench / profiling): which = bit 0 K9p point pass, bit 1 K9c
+// camera pass + finalize, bit 2 K8 cost pass, bit 3 skip the per-camera linearisation kernel (reuse
+// the table of the previous call). Reads d_cam / d_pts in place; outputs stay in the workspace.
+extern "C" int sfm_ba_linearise(const double *d_cam, const double *d_pts, const double *d_obs,
+                                const int32_t *d_cam_idx, const int32_t *d_pt_idx, int32_t n_cams,
+                                int32_t n_pts, int32_t n_obs, const double *h_K, int32_t which,
+                                int32_t reuse_index, void *d_ws, size_t ws_bytes, void *stream) {
+    if (!d_cam || !d_pts || !d_obs || !d_cam_idx || !d_pt_idx || !h_K) return SFM_E_INVALID;
+    BAPlan pl;
+    int rc = ba_prepare(pl, d_ws, ws_bytes, n_cams, n_pts, n_obs);
+    if (rc != SFM_OK) return rc;
+    cudaStream_t st = as_stream(stream);
+    KParam K;
+    for (int i = 0; i < 9; ++i) K.k[i] = h_K[i];
+    const double2 *obs = reinterpret_cast<const double2 *>(d_obs);
+    if ((rc = ba_acquire_index(pl, reuse_index != 0, d_ws, obs, d_cam_idx, d_pt_idx, n_cams, n_pts, n_obs, st)) != SFM_OK)
+        return rc;
+    if (!(which & 8) && (rc = launch_cam_linearise(pl, K, d_cam, pl.camlin[0], st)) != SFM_OK) return rc;
+    if (which & 1) {
+        if ((rc = launch_point_pass(pl, K, pl.camlin[0], d_pts, obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return rc;
+    }
+    if (which & 2) {
+        SFM_CUDA_TRY(cudaMemsetAsync(pl.gmax, 0, 8, st));
+        if (pl.nchunks) {
+            ba_camera_pass_kernel<<<pl.nchunks, 256, 0, st>>>(K, pl.camlin[0], d_pts, pl.obs_c, pl.pt_c, pl.chunk_cam,
+                                                              pl.chunk_beg, pl.chunk_end, pl.Upart);
+            SFM_LAUNCH_CHECK();
+        }
+        ba_cam_finalize_kernel<<<ceil_div(pl.nc, 128), 128, 0, st>>>(pl.Upart, pl.chunk_ptr, pl.nc, 1, pl.U, pl.gc, pl.Dc,
+                                                                     pl.gmax);
+        SFM_LAUNCH_CHECK();
+    }
+    if (which & 4) {
+        if ((rc = launch_cost(pl, pl.camlin[0], d_pts, obs, d_cam_idx, d_pt_idx, nullptr, st)) != SFM_OK) return rc;
+    }
     return SFM_OK;
 }
