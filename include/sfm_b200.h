@@ -185,6 +185,31 @@ int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, const int32_
                  const double *h_K, const sfm_ba_options *opts, sfm_ba_result *h_result,
                  void *d_ws, size_t ws_bytes, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Multi-GPU (one process per GPU). The library opens libnccl.so.2 with dlopen (the
+ * copy already in the process, e.g. torch's) -- SFM_E_NCCL when there is none. Rank 0 obtains a
+ * unique id, the host distributes its 128 bytes (torch.distributed / MPI / a file), every rank
+ * creates the communicator.
+ * ------------------------------------------------------------------------------------------ */
+const char *sfm_nccl_last_error(void);
+int sfm_nccl_unique_id(void *h_id128);
+int sfm_nccl_comm_create(const void *h_id128, int32_t rank, int32_t world, void **comm_out);
+int sfm_nccl_comm_destroy(void *comm);
+/* in-place all-reduces on that communicator (the F-RANSAC winner key: max over u64) */
+int sfm_allreduce_sum_f64(void *comm, double *d_buf, int64_t count, void *stream);
+int sfm_allreduce_max_u64(void *comm, uint64_t *d_buf, int64_t count, void *stream);
+
+/* Point-sharded bundle adjustment: this rank passes ALL cameras (replicated, identical on every
+ * rank) and a contiguous range of the points with all of their observations (local point indices
+ * 0..n_pts_local-1, sorted). Per linearisation U/g_c/cost are all-reduced, per trial step S/g_red
+ * and six scalars; every rank solves the camera system redundantly and ends with identical
+ * cameras and results. world == 1 (comm may be null) is sfm_ba_solve. */
+int sfm_ba_solve_mgpu(double *d_cam, double *d_pts_local, const double *d_obs_local,
+                      const int32_t *d_cam_idx_local, const int32_t *d_pt_idx_local, int32_t n_cams,
+                      int32_t n_pts_local, int32_t n_obs_local, const double *h_K,
+                      const sfm_ba_options *opts, sfm_ba_result *h_result, void *d_ws, size_t ws_bytes,
+                      void *comm, int32_t rank, int32_t world, void *stream);
+
 /* One linearisation pass in isolation, for bench.py / ncu (the passes of sfm_ba_solve, same kernels):
  * which = bit 0 point pass K9p (W, V, g_p, cost partials), bit 1 camera pass K9c (U, g_c), bit 2 cost
  * pass K8, bit 3 reuse the linearised-camera table of the previous call. Outputs stay in d_ws. */

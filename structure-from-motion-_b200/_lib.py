@@ -48,6 +48,14 @@ SIGNATURES = {
                                    c_vp, c_f64p, c_f64p, c_vp, C.c_size_t, c_vp]),
     "sfm_ba_solve": (C.c_int, [c_f64p, c_f64p, c_f64p, c_i32p, c_i32p, C.c_int32, C.c_int32, C.c_int32,
                                c_vp, c_vp, c_vp, c_vp, C.c_size_t, c_vp]),
+    "sfm_ba_solve_mgpu": (C.c_int, [c_f64p, c_f64p, c_f64p, c_i32p, c_i32p, C.c_int32, C.c_int32, C.c_int32,
+                                    c_vp, c_vp, c_vp, c_vp, C.c_size_t, c_vp, C.c_int32, C.c_int32, c_vp]),
+    "sfm_nccl_last_error": (C.c_char_p, []),
+    "sfm_nccl_unique_id": (C.c_int, [c_vp]),
+    "sfm_nccl_comm_create": (C.c_int, [c_vp, C.c_int32, C.c_int32, c_vp]),
+    "sfm_nccl_comm_destroy": (C.c_int, [c_vp]),
+    "sfm_allreduce_sum_f64": (C.c_int, [c_vp, c_f64p, C.c_int64, c_vp]),
+    "sfm_allreduce_max_u64": (C.c_int, [c_vp, c_vp, C.c_int64, c_vp]),
     "sfm_ba_linearise": (C.c_int, [c_f64p, c_f64p, c_f64p, c_i32p, c_i32p, C.c_int32, C.c_int32, C.c_int32,
                                    c_vp, C.c_int32, C.c_int32, c_vp, C.c_size_t, c_vp]),
     "sfm_chol_solve_workspace_bytes": (C.c_size_t, [C.c_int32]),
@@ -112,6 +120,8 @@ def load(build_if_missing: bool = True):
 def check(rc: int, what: str):
     if rc != 0:
         msg = load().sfm_last_cuda_error().decode(errors="replace") if rc == 2 else ""
+        if rc == 4:
+            msg = load().sfm_nccl_last_error().decode(errors="replace")
         raise SfmError(f"{what} failed: {_ERR.get(rc, rc)} {msg}")
 
 

@@ -284,12 +284,9 @@ ba_camera_pass_kernel(KParam K, const double *__restrict__ camlin, const double 
     }
 }
 
-// Sum the chunk partials of every camera in chunk order -> U [nc,21], gc [nc,6]; update the
-// MINPACK scaling Dc (first linearisation: column norm, 1 if zero; later: running max) and
-// the gtol numerator max_j |g_j| / |J_j|.
+// Sum the chunk partials of every camera in chunk order -> U [nc,21], g_c [nc,6] (this rank's share).
 __global__ void ba_cam_finalize_kernel(const double *__restrict__ Upart, const int32_t *__restrict__ chunk_ptr,
-                                       int nc, int first, double *__restrict__ U, double *__restrict__ gc,
-                                       double *__restrict__ Dc, unsigned long long *__restrict__ gmax) {
+                                       int nc, double *__restrict__ U, double *__restrict__ gc) {
     int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= nc) return;
     double acc[27];
@@ -300,14 +297,23 @@ __global__ void ba_cam_finalize_kernel(const double *__restrict__ Upart, const i
         for (int i = 0; i < 27; ++i) acc[i] += Upart[(size_t)ch * 27 + i];
 #pragma unroll
     for (int i = 0; i < 21; ++i) U[(size_t)c * 21 + i] = acc[i];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) gc[(size_t)c * 6 + j] = acc[21 + j];
+}
+
+// From the (all-rank) U, g_c: the MINPACK scaling Dc (first linearisation: column norm, 1 if zero;
+// later: running max) and the gtol numerator max_j |g_j| / |J_j|.
+__global__ void ba_cam_scale_kernel(const double *__restrict__ U, const double *__restrict__ gc, int nc, int first,
+                                    double *__restrict__ Dc, unsigned long long *__restrict__ gmax) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= nc) return;
     double gm = 0.0;
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
-        gc[(size_t)c * 6 + j] = acc[21 + j];
-        double cn = sqrt(acc[sym_idx(j, j)]);
+        double cn = sqrt(U[(size_t)c * 21 + sym_idx(j, j)]);
         double d = first ? (cn == 0.0 ? 1.0 : cn) : fmax(Dc[(size_t)c * 6 + j], cn);
         Dc[(size_t)c * 6 + j] = d;
-        if (cn > 0.0) gm = fmax(gm, fabs(acc[21 + j]) / cn);
+        if (cn > 0.0) gm = fmax(gm, fabs(gc[(size_t)c * 6 + j]) / cn);
     }
     atomic_max_pos(gmax, gm);
 }
@@ -318,6 +324,7 @@ __global__ void ba_cam_finalize_kernel(const double *__restrict__ Upart, const i
 __global__ void ba_schur_init_kernel(const double *__restrict__ U, const double *__restrict__ gc,
                                      const double *__restrict__ Dc, int nc, int npad, size_t ld,
                                      double lambda, double *__restrict__ S) {
+    // (multi-GPU: launched on rank 0 only -- the camera blocks enter the all-reduced S once)
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int n = 6 * nc;
     if (t < nc * 36) {
@@ -469,7 +476,7 @@ ba_schur_kernel(const double *__restrict__ W, int nobs, const int32_t *__restric
 // partial sums layout (4 doubles): [s.g, |D s|^2, |D x_new|^2, |D x_cur|^2]
 __global__ void __launch_bounds__(256)
 ba_update_cams_kernel(const double *__restrict__ cam, const double *__restrict__ dc, const double *__restrict__ gc,
-                      const double *__restrict__ Dc, int n, double *__restrict__ cam_new,
+                      const double *__restrict__ Dc, int n, int contribute, double *__restrict__ cam_new,
                       double *__restrict__ part) {
     __shared__ double sred[32];
     double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
@@ -482,7 +489,11 @@ ba_update_cams_kernel(const double *__restrict__ cam, const double *__restrict__
         a3 += (d * x) * (d * x);
     }
     a0 = block_sum(a0, sred); a1 = block_sum(a1, sred); a2 = block_sum(a2, sred); a3 = block_sum(a3, sred);
-    if (threadIdx.x == 0) { part[0] = a0; part[1] = a1; part[2] = a2; part[3] = a3; }
+    if (threadIdx.x == 0) {
+        // multi-GPU: every rank updates the replicated cameras, one rank reports their sums
+        part[0] = contribute ? a0 : 0.0; part[1] = contribute ? a1 : 0.0;
+        part[2] = contribute ? a2 : 0.0; part[3] = contribute ? a3 : 0.0;
+    }
 }
 
 // tp[p] = sum over the observations of p of W_o^T dc[cam(o)]   (thread per observation)
@@ -547,7 +558,8 @@ ba_update_points_kernel(const double *__restrict__ pts, const double *__restrict
     }
 }
 
-// out[0] = sum costpart; out[1..4] = sum of the update partials; out[5] = gmax; out[6] = flags
+// out[0] = sum costpart; out[1..4] = sum of the update partials; out[5] = point-block failure (0/1);
+// out[6] = gmax; out[7] = Cholesky failure (0/1). out[0..5] are summed across ranks, out[6..7] are not.
 __global__ void __launch_bounds__(256)
 ba_reduce_scalars_kernel(const double *__restrict__ costpart, int ncost, const double *__restrict__ updpart,
                          int nupd, const unsigned long long *__restrict__ gmax, const int *__restrict__ fail_s,
@@ -565,8 +577,9 @@ ba_reduce_scalars_kernel(const double *__restrict__ costpart, int ncost, const d
         out[0] = c;
 #pragma unroll
         for (int q = 0; q < 4; ++q) out[1 + q] = a[q];
-        out[5] = gmax ? __longlong_as_double((long long)*gmax) : 0.0;
-        out[6] = (double)((fail_s ? *fail_s : 0) | (fail_c ? (*fail_c ? 4 : 0) : 0));
+        out[5] = (fail_s && *fail_s) ? 1.0 : 0.0;
+        out[6] = gmax ? __longlong_as_double((long long)*gmax) : 0.0;
+        out[7] = (fail_c && *fail_c) ? 1.0 : 0.0;
     }
 }
 
@@ -583,7 +596,7 @@ struct BAPlan {
     // state
     double *cam[2], *pts[2], *camlin[2];
     double *W, *V, *gp, *Vinv, *bp, *tp, *U, *gc, *Upart, *Dc, *Dp, *S, *Linv, *dc;
-    double *costpart, *updpart, *scal;
+    double *costpart, *updpart, *scal, *red1;
     unsigned long long *gmax;
     int *flags;       // [0] index validation, [1] schur (vinv) failure, [2] cholesky failure
 };
@@ -643,8 +656,9 @@ static size_t ba_layout(BAPlan &pl, unsigned char *base, int nc, int np, int nob
     CARVE(Vinv, double, D * 6 * np);
     CARVE(bp, double, D * 3 * np);
     CARVE(tp, double, D * 3 * np);
-    CARVE(U, double, D * 21 * nc);
-    CARVE(gc, double, D * 6 * nc);
+    CARVE(U, double, D * (27 * nc + 8));   // [U 21nc | g_c 6nc | cost, ...]: ONE allreduce per linearisation
+    pl.gc = pl.U + 21 * (size_t)nc;
+    pl.red1 = pl.gc + 6 * (size_t)nc;
     CARVE(Upart, double, D * 27 * max_chunks);
     CARVE(Dc, double, D * 6 * nc);
     CARVE(Dp, double, D * 3 * np);
@@ -855,10 +869,19 @@ extern "C" int sfm_ba_residuals(const double *d_cam, const double *d_pts, const 
     return SFM_OK;
 }
 
-extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, const int32_t *d_cam_idx,
-                            const int32_t *d_pt_idx, int32_t n_cams, int32_t n_pts, int32_t n_obs,
-                            const double *h_K, const sfm_ba_options *opts, sfm_ba_result *h_result,
-                            void *d_ws, size_t ws_bytes, void *stream) {
+namespace sfm {
+int comm_allreduce_sum_f64(void *comm, double *buf, size_t count, cudaStream_t st);
+int comm_allreduce_max_u64(void *comm, unsigned long long *buf, size_t count, cudaStream_t st);
+}
+
+// The LM driver. comm == nullptr: single GPU. Otherwise this rank holds a contiguous range of the
+// points (with all of their observations, local point indices) and ALL cameras; U/g_c/cost are
+// all-reduced per linearisation, S/g_red and six scalars per trial step, and every rank runs the
+// camera solve redundantly on identical bits.
+static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, const int32_t *d_cam_idx,
+                         const int32_t *d_pt_idx, int32_t n_cams, int32_t n_pts, int32_t n_obs,
+                         const double *h_K, const sfm_ba_options *opts, sfm_ba_result *h_result,
+                         void *d_ws, size_t ws_bytes, void *stream, void *comm, int rank) {
     if (!d_cam || !d_pts || !d_obs || !d_cam_idx || !d_pt_idx || !h_K || !h_result) return SFM_E_INVALID;
     sfm_ba_options o;
     if (opts) o = *opts; else sfm_ba_default_options(&o);
@@ -890,17 +913,19 @@ extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, c
                                                               pl.chunk_cam, pl.chunk_beg, pl.chunk_end, pl.Upart);
             SFM_LAUNCH_CHECK();
         }
-        ba_cam_finalize_kernel<<<ceil_div(nc, 128), 128, 0, st>>>(pl.Upart, pl.chunk_ptr, nc, first, pl.U, pl.gc,
-                                                                  pl.Dc, pl.gmax);
+        ba_cam_finalize_kernel<<<ceil_div(nc, 128), 128, 0, st>>>(pl.Upart, pl.chunk_ptr, nc, pl.U, pl.gc);
+        SFM_LAUNCH_CHECK();
+        ba_reduce_scalars_kernel<<<1, 256, 0, st>>>(pl.costpart, pl.grid_obs, nullptr, 0, nullptr, nullptr, nullptr, pl.red1);
+        SFM_LAUNCH_CHECK();
+        if ((r = comm_allreduce_sum_f64(comm, pl.U, 27 * (size_t)nc + 1, st)) != SFM_OK) return r;
+        ba_cam_scale_kernel<<<ceil_div(nc, 128), 128, 0, st>>>(pl.U, pl.gc, nc, first, pl.Dc, pl.gmax);
         SFM_LAUNCH_CHECK();
         return SFM_OK;
     };
 
     if ((rc = launch_cam_linearise(pl, K, pl.cam[0], pl.camlin[0], st)) != SFM_OK) return rc;
     if ((rc = linearise(1)) != SFM_OK) return rc;
-    ba_reduce_scalars_kernel<<<1, 256, 0, st>>>(pl.costpart, pl.grid_obs, nullptr, 0, nullptr, nullptr, nullptr, pl.scal);
-    SFM_LAUNCH_CHECK();
-    SFM_CUDA_TRY(cudaMemcpyAsync(h_scal, pl.scal, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    SFM_CUDA_TRY(cudaMemcpyAsync(h_scal, pl.red1, sizeof(double), cudaMemcpyDeviceToHost, st));
     SFM_CUDA_TRY(cudaStreamSynchronize(st));
     double cost = h_scal[0];
     h_result->cost0 = h_result->cost = cost;
@@ -918,9 +943,11 @@ extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, c
         SFM_CUDA_TRY(cudaMemsetAsync(pl.S, 0, s_bytes, st));
         SFM_CUDA_TRY(cudaMemsetAsync(pl.flags + 1, 0, 2 * sizeof(int), st));
         SFM_CUDA_TRY(cudaMemsetAsync(pl.tp, 0, sizeof(double) * 3 * (size_t)np, st));
-        ba_schur_init_kernel<<<ceil_div(std::max(nc * 36, pl.npad), 256), 256, 0, st>>>(pl.U, pl.gc, pl.Dc, nc, pl.npad,
-                                                                                       pl.ld, lambda, pl.S);
-        SFM_LAUNCH_CHECK();
+        if (rank == 0) {      // the camera blocks U + lambda Dc^2, g_c and the padding enter the summed S once
+            ba_schur_init_kernel<<<ceil_div(std::max(nc * 36, pl.npad), 256), 256, 0, st>>>(pl.U, pl.gc, pl.Dc, nc, pl.npad,
+                                                                                           pl.ld, lambda, pl.S);
+            SFM_LAUNCH_CHECK();
+        }
         {
             int grid = std::max(1, std::min(sm_count() * 8, ceil_div(np, SCH_WARPS)));
             ba_schur_kernel<<<grid, SCH_WARPS * 32, 0, st>>>(pl.W, nobs, d_cam_idx, pl.pt_ptr, np, pl.V, pl.gp, pl.Dp,
@@ -928,9 +955,11 @@ extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, c
                                                              pl.S + (size_t)pl.npad * pl.ld, pl.gmax, pl.flags + 1);
             SFM_LAUNCH_CHECK();
         }
+        if ((rc = comm_allreduce_sum_f64(comm, pl.S, (size_t)(pl.npad + BA_NB) * pl.ld, st)) != SFM_OK) return rc;
+        if (update_D && (rc = comm_allreduce_max_u64(comm, pl.gmax, 1, st)) != SFM_OK) return rc;
         if ((rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st, nullptr)) != SFM_OK) return rc;
         const int nxt = cur ^ 1;
-        ba_update_cams_kernel<<<1, 256, 0, st>>>(pl.cam[cur], pl.dc, pl.gc, pl.Dc, n, pl.cam[nxt], pl.updpart);
+        ba_update_cams_kernel<<<1, 256, 0, st>>>(pl.cam[cur], pl.dc, pl.gc, pl.Dc, n, rank == 0, pl.cam[nxt], pl.updpart);
         SFM_LAUNCH_CHECK();
         ba_point_rhs_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(pl.W, nobs, d_cam_idx, d_pt_idx, pl.pt_ptr, pl.dc, pl.tp);
         SFM_LAUNCH_CHECK();
@@ -942,12 +971,13 @@ extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, c
         ba_reduce_scalars_kernel<<<1, 256, 0, st>>>(pl.costpart, pl.grid_obs, pl.updpart, pl.grid_pts + 1, pl.gmax,
                                                     pl.flags + 1, pl.flags + 2, pl.scal);
         SFM_LAUNCH_CHECK();
+        if ((rc = comm_allreduce_sum_f64(comm, pl.scal, 6, st)) != SFM_OK) return rc;
         SFM_CUDA_TRY(cudaMemcpyAsync(h_scal, pl.scal, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
         SFM_CUDA_TRY(cudaStreamSynchronize(st));
         ++trials;
         const double cost_new = h_scal[0], sg = h_scal[1], Ds2 = h_scal[2], Dx2n = h_scal[3], Dx2c = h_scal[4];
-        const double gmax = h_scal[5];
-        const int fail = (int)h_scal[6];
+        const double gmax = h_scal[6];
+        const int fail = (h_scal[5] != 0.0 ? 2 : 0) | (h_scal[7] != 0.0 ? 4 : 0);
         const double fnorm2 = 2.0 * cost;
         if (update_D) {
             // MINPACK gtol test (lmder, top of the outer loop): max_j |J_j^T f| / (|J_j| |f|)
@@ -1007,6 +1037,24 @@ extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, c
     return SFM_OK;
 }
 
+extern "C" int sfm_ba_solve(double *d_cam, double *d_pts, const double *d_obs, const int32_t *d_cam_idx,
+                            const int32_t *d_pt_idx, int32_t n_cams, int32_t n_pts, int32_t n_obs,
+                            const double *h_K, const sfm_ba_options *opts, sfm_ba_result *h_result,
+                            void *d_ws, size_t ws_bytes, void *stream) {
+    return ba_solve_impl(d_cam, d_pts, d_obs, d_cam_idx, d_pt_idx, n_cams, n_pts, n_obs, h_K, opts, h_result, d_ws,
+                         ws_bytes, stream, nullptr, 0);
+}
+
+extern "C" int sfm_ba_solve_mgpu(double *d_cam, double *d_pts_local, const double *d_obs_local,
+                                 const int32_t *d_cam_idx_local, const int32_t *d_pt_idx_local, int32_t n_cams,
+                                 int32_t n_pts_local, int32_t n_obs_local, const double *h_K,
+                                 const sfm_ba_options *opts, sfm_ba_result *h_result, void *d_ws, size_t ws_bytes,
+                                 void *comm, int32_t rank, int32_t world, void *stream) {
+    if (world < 1 || rank < 0 || rank >= world || (world > 1 && !comm)) return SFM_E_INVALID;
+    return ba_solve_impl(d_cam, d_pts_local, d_obs_local, d_cam_idx_local, d_pt_idx_local, n_cams, n_pts_local,
+                         n_obs_local, h_K, opts, h_result, d_ws, ws_bytes, stream, world > 1 ? comm : nullptr, rank);
+}
+
 // One linearisation pass in isolation (bench / profiling): which = bit 0 K9p point pass, bit 1 K9c
 // camera pass + finalize, bit 2 K8 cost pass, bit 3 skip the per-camera linearisation kernel (reuse
 // the table of the previous call). Reads d_cam / d_pts in place; outputs stay in the workspace.
@@ -1035,8 +1083,9 @@ extern "C" int sfm_ba_linearise(const double *d_cam, const double *d_pts, const 
                                                               pl.chunk_beg, pl.chunk_end, pl.Upart);
             SFM_LAUNCH_CHECK();
         }
-        ba_cam_finalize_kernel<<<ceil_div(pl.nc, 128), 128, 0, st>>>(pl.Upart, pl.chunk_ptr, pl.nc, 1, pl.U, pl.gc, pl.Dc,
-                                                                     pl.gmax);
+        ba_cam_finalize_kernel<<<ceil_div(pl.nc, 128), 128, 0, st>>>(pl.Upart, pl.chunk_ptr, pl.nc, pl.U, pl.gc);
+        SFM_LAUNCH_CHECK();
+        ba_cam_scale_kernel<<<ceil_div(pl.nc, 128), 128, 0, st>>>(pl.U, pl.gc, pl.nc, 1, pl.Dc, pl.gmax);
         SFM_LAUNCH_CHECK();
     }
     if (which & 4) {
