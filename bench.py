@@ -242,6 +242,10 @@ def run_ours(args, rank, world):
            "steps": e2e_steps}
 
     best = r.best.cpu().numpy()
+    ba_mgpu = None
+    if world > 1 and not args.skip_ba:
+        import bench_ba
+        ba_mgpu = bench_ba.run_sharded(args, rank, world, flush)
     if rank == 0:
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
@@ -260,6 +264,9 @@ def run_ours(args, rank, world):
                 out["ba"] = bench_ba.run_single_gpu(args, peaks, peak_src, flush)
                 out["ba"]["cpu_baseline"] = bench_ba.cpu_baseline()
                 out["gpu_launches"] += out["ba"]["gpu_launches"]
+        if ba_mgpu is not None:
+            out["ba"] = ba_mgpu
+            out["gpu_launches"] += ba_mgpu["gpu_launches"]
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

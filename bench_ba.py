@@ -176,3 +176,48 @@ def run_single_gpu(args, peaks, peak_src, flush):
                        "note": "168 B per observation + 168 B per point (DESIGN.md); timed alone with CUDA events, "
                                "includes the 36 MB memset of V/g_p and the per-camera linearisation reuse"}
     return out
+
+
+def run_sharded(args, rank, world, flush):
+    """N > 1: BASELINE configs[4] (C5) sharded by point across the ranks; strong scaling (the problem
+    is fixed, each rank holds 1/N of the points). Time = max over ranks of the CUDA-event time."""
+    import torch
+    import torch.distributed as dist
+    from sfm_b200 import _lib, bundle_mgpu, device
+    comm = bundle_mgpu.NcclComm(rank, world)
+    sc, cams0, pts0 = _scene(C5)
+    prob = bundle_mgpu.BAShardedProblem(C5["n_cams"], C5["n_pts"], sc["cam_idx"], sc["pt_idx"], sc["obs"], sc["K"], comm)
+    d_cam0, d_pts0 = device.to_device(cams0), device.to_device(pts0[prob.p_lo:prob.p_hi])
+    d_cam, d_pts = torch.empty_like(d_cam0), torch.empty_like(d_pts0)
+    steps = max(3, min(args.steps, 5))
+    for _ in range(2):
+        d_cam.copy_(d_cam0); d_pts.copy_(d_pts0)
+        prob.solve_device(d_cam, d_pts)
+    dist.barrier(); torch.cuda.synchronize()
+    l0 = _lib.launch_count()
+    ev, infos = [], []
+    for _ in range(steps):
+        flush.zero_()
+        d_cam.copy_(d_cam0); d_pts.copy_(d_pts0)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        infos.append(prob.solve_device(d_cam, d_pts))
+        b.record()
+        ev.append((a, b))
+    dist.barrier(); torch.cuda.synchronize()
+    t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    its = sum(i["n_linearisations"] for i in infos)
+    n5 = len(sc["obs"])
+    out = {"metric": "BA LM iterations/sec", "unit": "LM iterations/s", "dtype": "f64", "scaling": "strong",
+           "value": its / (ms * 1e-3), "ms_per_solve": ms / steps, "solves": steps, "n_gpus": world,
+           "config": {"workload": "C5 synthetic BAL-scale BA sharded by point: " + _name(C5),
+                      "points_per_rank": prob.n_pts, "observations_per_rank": prob.n_obs,
+                      "collectives_per_trial": "all-reduce S+g_red (%.0f MB), 6 scalars, gmax; per linearisation U|g_c|cost"
+                                               % ((6000 + 48) * 6000 * 8 / 1e6)},
+           "lm_iterations_per_solve": its / steps, "cost": infos[-1]["cost"],
+           "rmse_px": float(np.sqrt(2 * infos[-1]["cost"] / n5)), "status": infos[-1]["status"],
+           "gpu_launches": int(_lib.launch_count() - l0)}
+    comm.destroy()
+    return out

@@ -31,6 +31,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <mutex>
 #include <vector>
@@ -222,32 +223,44 @@ ba_cost_kernel(const double *__restrict__ camlin, int nc, const double *__restri
     }
     double cost = 0.0;
     const int stride = gridDim.x * THREADS;
-    for (int o = blockIdx.x * THREADS + threadIdx.x; o < nobs; o += stride) {
+    // two observations in flight per thread: the pass is latency bound (16 warps per SM when the
+    // camera table fills shared memory), so the loads of both are issued before either is used
+    for (int o = blockIdx.x * THREADS + threadIdx.x; o < nobs; o += 2 * stride) {
+        const int o2 = o + stride;
+        const bool two = o2 < nobs;
         const int c = cam_idx[o], p = pt_idx[o];
-        const double2 ob = obs[o];
+        const int c2 = two ? cam_idx[o2] : c, p2 = two ? pt_idx[o2] : p;
+        const double2 ob = obs[o], ob2 = obs[two ? o2 : o];
         double X[3] = {pts[3 * (size_t)p], pts[3 * (size_t)p + 1], pts[3 * (size_t)p + 2]};
-        const double *cp = ctab + (size_t)CAMLIN_STRIDE * c;
-        CamLin cl;
+        double X2[3] = {pts[3 * (size_t)p2], pts[3 * (size_t)p2 + 1], pts[3 * (size_t)p2 + 2]};
+        CamLin cl, cl2;
+        const double *cp = ctab + (size_t)CAMLIN_STRIDE * c, *cp2 = ctab + (size_t)CAMLIN_STRIDE * c2;
 #pragma unroll
-        for (int i = 0; i < 9; ++i) cl.M[i] = cp[i];
+        for (int i = 0; i < 9; ++i) { cl.M[i] = cp[i]; cl2.M[i] = cp2[i]; }
 #pragma unroll
-        for (int i = 0; i < 3; ++i) cl.kt[i] = cp[9 + i];
-        double ru, rv;
+        for (int i = 0; i < 3; ++i) { cl.kt[i] = cp[9 + i]; cl2.kt[i] = cp2[9 + i]; }
+        double ru, rv, ru2, rv2;
         ba_residual_only(cl, X, ob.x, ob.y, ru, rv);
+        ba_residual_only(cl2, X2, ob2.x, ob2.y, ru2, rv2);
         cost += 0.5 * (ru * ru + rv * rv);
         if (r_out) r_out[o] = make_double2(ru, rv);
+        if (two) {
+            cost += 0.5 * (ru2 * ru2 + rv2 * rv2);
+            if (r_out) r_out[o2] = make_double2(ru2, rv2);
+        }
     }
     double s = block_sum(cost, sred);
     if (threadIdx.x == 0) costpart[blockIdx.x] = s;
 }
 
 // K9c. One CTA per (camera, chunk of its observations) in camera-major order.
-__global__ void __launch_bounds__(256)
+constexpr int K9C_THREADS = 128;
+__global__ void __launch_bounds__(K9C_THREADS, 4)
 ba_camera_pass_kernel(KParam K, const double *__restrict__ camlin, const double *__restrict__ pts,
                       const double2 *__restrict__ obs_c, const int32_t *__restrict__ pt_c,
                       const int32_t *__restrict__ chunk_cam, const int32_t *__restrict__ chunk_beg,
                       const int32_t *__restrict__ chunk_end, double *__restrict__ Upart) {
-    __shared__ double sred[8][27];
+    __shared__ double sred[K9C_THREADS / 32][27];
     const int ch = blockIdx.x;
     const int c = chunk_cam[ch], beg = chunk_beg[ch], end = chunk_end[ch];
     CamLin cl;
@@ -255,7 +268,7 @@ ba_camera_pass_kernel(KParam K, const double *__restrict__ camlin, const double 
     double acc[27];
 #pragma unroll
     for (int i = 0; i < 27; ++i) acc[i] = 0.0;
-    for (int o = beg + threadIdx.x; o < end; o += 256) {
+    for (int o = beg + threadIdx.x; o < end; o += K9C_THREADS) {
         const int p = pt_c[o];
         const double2 ob = obs_c[o];
         double X[3] = {pts[3 * (size_t)p], pts[3 * (size_t)p + 1], pts[3 * (size_t)p + 2]};
@@ -279,7 +292,7 @@ ba_camera_pass_kernel(KParam K, const double *__restrict__ camlin, const double 
     if (threadIdx.x < 27) {
         double s = 0.0;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) s += sred[w][threadIdx.x];
+        for (int w = 0; w < K9C_THREADS / 32; ++w) s += sred[w][threadIdx.x];
         Upart[(size_t)ch * 27 + threadIdx.x] = s;
     }
 }
@@ -625,8 +638,9 @@ static size_t ba_layout(BAPlan &pl, unsigned char *base, int nc, int np, int nob
     const int sms = sm_count();
     pl.cam_smem = (size_t)nc * CAMLIN_STRIDE * sizeof(double);
     pl.smem_cams = pl.cam_smem <= BA_SMEM_CAM_LIMIT;
-    pl.obs_threads = (pl.smem_cams && pl.cam_smem > 100 * 1024) ? 512 : 256;
-    int per_sm = pl.obs_threads == 512 ? 1 : 2;
+    // a camera table above ~100 KB leaves room for one CTA per SM: make it a wide one (24 warps)
+    pl.obs_threads = (pl.smem_cams && pl.cam_smem > 100 * 1024) ? 768 : 256;
+    int per_sm = pl.obs_threads == 768 ? 1 : 2;
     pl.grid_obs = std::max(1, std::min(sms * per_sm, ceil_div(nobs, pl.obs_threads)));
     pl.grid_pts = std::max(1, std::min(sms * 4, ceil_div(np, 256)));
     const int max_chunks = nobs / BA_CHUNK + nc + 1;
@@ -677,9 +691,9 @@ static size_t ba_layout(BAPlan &pl, unsigned char *base, int nc, int np, int nob
 template <bool SM>
 static void set_obs_kernel_attrs(size_t smem) {
     cudaFuncSetAttribute(ba_point_pass_kernel<SM, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(ba_point_pass_kernel<SM, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(ba_point_pass_kernel<SM, 768, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(ba_cost_kernel<SM, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(ba_cost_kernel<SM, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(ba_cost_kernel<SM, 768, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
 
 static int launch_point_pass(const BAPlan &pl, const KParam &K, const double *camlin, const double *pts,
@@ -688,7 +702,7 @@ static int launch_point_pass(const BAPlan &pl, const KParam &K, const double *ca
     const size_t sm = pl.smem_cams ? pl.cam_smem : 0;
 #define PP_ARGS K, camlin, pl.nc, pts, obs, cam_idx, pt_idx, pl.pt_ptr, pl.nobs, pl.W, pl.V, pl.gp, pl.costpart
     if (pl.smem_cams) {
-        if (pl.obs_threads == 512) ba_point_pass_kernel<true, 512, 1><<<pl.grid_obs, 512, sm, st>>>(PP_ARGS);
+        if (pl.obs_threads == 768) ba_point_pass_kernel<true, 768, 1><<<pl.grid_obs, 768, sm, st>>>(PP_ARGS);
         else ba_point_pass_kernel<true, 256, 2><<<pl.grid_obs, 256, sm, st>>>(PP_ARGS);
     } else {
         ba_point_pass_kernel<false, 256, 2><<<pl.grid_obs, 256, 0, st>>>(PP_ARGS);
@@ -703,7 +717,7 @@ static int launch_cost(const BAPlan &pl, const double *camlin, const double *pts
     const size_t sm = pl.smem_cams ? pl.cam_smem : 0;
 #define C_ARGS camlin, pl.nc, pts, obs, cam_idx, pt_idx, pl.nobs, pl.costpart, r_out
     if (pl.smem_cams) {
-        if (pl.obs_threads == 512) ba_cost_kernel<true, 512, 1><<<pl.grid_obs, 512, sm, st>>>(C_ARGS);
+        if (pl.obs_threads == 768) ba_cost_kernel<true, 768, 1><<<pl.grid_obs, 768, sm, st>>>(C_ARGS);
         else ba_cost_kernel<true, 256, 2><<<pl.grid_obs, 256, sm, st>>>(C_ARGS);
     } else {
         ba_cost_kernel<false, 256, 2><<<pl.grid_obs, 256, 0, st>>>(C_ARGS);
@@ -909,7 +923,7 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
         SFM_CUDA_TRY(cudaMemsetAsync(pl.gmax, 0, 8, st));
         if ((r = launch_point_pass(pl, K, pl.camlin[cur], pl.pts[cur], obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return r;
         if (pl.nchunks) {
-            ba_camera_pass_kernel<<<pl.nchunks, 256, 0, st>>>(K, pl.camlin[cur], pl.pts[cur], pl.obs_c, pl.pt_c,
+            ba_camera_pass_kernel<<<pl.nchunks, K9C_THREADS, 0, st>>>(K, pl.camlin[cur], pl.pts[cur], pl.obs_c, pl.pt_c,
                                                               pl.chunk_cam, pl.chunk_beg, pl.chunk_end, pl.Upart);
             SFM_LAUNCH_CHECK();
         }
@@ -1079,7 +1093,7 @@ extern "C" int sfm_ba_linearise(const double *d_cam, const double *d_pts, const 
     if (which & 2) {
         SFM_CUDA_TRY(cudaMemsetAsync(pl.gmax, 0, 8, st));
         if (pl.nchunks) {
-            ba_camera_pass_kernel<<<pl.nchunks, 256, 0, st>>>(K, pl.camlin[0], d_pts, pl.obs_c, pl.pt_c, pl.chunk_cam,
+            ba_camera_pass_kernel<<<pl.nchunks, K9C_THREADS, 0, st>>>(K, pl.camlin[0], d_pts, pl.obs_c, pl.pt_c, pl.chunk_cam,
                                                               pl.chunk_beg, pl.chunk_end, pl.Upart);
             SFM_LAUNCH_CHECK();
         }
