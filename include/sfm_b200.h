@@ -111,6 +111,12 @@ int sfm_fundamental_npt(const double *d_x1, const double *d_x2, int32_t n, doubl
  * as tightly as the reference).
  * ------------------------------------------------------------------------------------------ */
 
+/* N1: LinearTriangulation (LinearTriangulation.py:3-92) for n points and ONE camera pair: the DLT
+ * null vector of the 4x4 system per point, de-homogenised when |X~[3]| > 1e-8. h_P1,h_P2: HOST 3x4
+ * projection matrices K[R|-RC]; d_x1,d_x2 [n,2]; d_X [n,3] out. */
+int sfm_lintri(const double *h_P1, const double *h_P2, const double *d_x1, const double *d_x2,
+               int32_t n, double *d_X, void *stream);
+
 /* K5: NonLinearTriangulation (NonLinearTriangulation.py:53-130) for n points and ONE camera
  * pair. h_P1,h_P2: HOST 3x4 projection matrices K[R|-RC] (row-major, 12 doubles each).
  * d_x1,d_x2 [n,2]; d_X0 [n,3] initial points; d_X [n,3] out (may alias d_X0);

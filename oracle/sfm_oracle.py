@@ -289,3 +289,20 @@ def pnp_ransac(X, x, K, threshold=200, n_max=1000, samples=None):
         except Exception as e:
             raise ValueError(f"PnP estimation failed: {e}")
     return d["poses"][d["best_idx"]]
+
+
+# ----------------------------------------------------------------------------------------------
+# Linear triangulation: LinearTriangulation.py:3-92 (pinned by tests/golden/nltri.npz "x0")
+# ----------------------------------------------------------------------------------------------
+def linear_triangulation(K, C1, R1, C2, R2, x1, x2):
+    K, C1, R1, C2, R2 = (np.array(a, float) for a in (K, C1, R1, C2, R2))
+    x1, x2 = np.array(x1, float), np.array(x2, float)
+    P1 = K @ np.hstack([R1, -R1 @ C1.reshape(3, 1)])               # :44-50
+    P2 = K @ np.hstack([R2, -R2 @ C2.reshape(3, 1)])
+    out = []
+    for (u1, v1), (u2, v2) in zip(x1, x2):
+        A = np.stack([v1 * P1[2] - P1[1], P1[0] - u1 * P1[2],      # :76-81
+                      v2 * P2[2] - P2[1], P2[0] - u2 * P2[2]])
+        Xh = np.linalg.svd(A)[2][-1]                               # :84-85
+        out.append(Xh[:3] / Xh[3] if abs(Xh[3]) > 1e-8 else Xh[:3])   # :88-92
+    return np.array(out)

@@ -29,6 +29,38 @@ def projection_matrix(K, C_, R):
 
 
 # ---------------------------------------------------------------------------------------------
+# LinearTriangulation.py (it produces x0 for every NonLinearTriangulation call)
+# ---------------------------------------------------------------------------------------------
+def lintri_device(P1, P2, d_x1, d_x2):
+    """N1 on device tensors -> d_X [n,3]."""
+    n = int(d_x1.shape[0])
+    d_X = device.empty((n, 3), torch.float64)
+    P1 = np.ascontiguousarray(P1, np.float64)
+    P2 = np.ascontiguousarray(P2, np.float64)
+    rc = _lib.load().sfm_lintri(_hptr(P1), _hptr(P2), device.ptr(d_x1), device.ptr(d_x2), n, device.ptr(d_X),
+                                device.stream())
+    _lib.check(rc, "sfm_lintri")
+    return d_X
+
+
+def LinearTriangulation(K, C1, R1, C2, R2, x1, x2):
+    """Drop-in for LinearTriangulation.py:3-92 -> points (N x 3)."""
+    x1 = np.array(x1)
+    x2 = np.array(x2)
+    n_points = len(x1)
+    if n_points == 0:
+        return np.array([])
+    P1, P2 = projection_matrix(K, C1, R1), projection_matrix(K, C2, R2)
+    d_X = lintri_device(P1, P2, device.to_device(x1.reshape(n_points, 2)), device.to_device(x2.reshape(n_points, 2)))
+    return d_X.cpu().numpy()
+
+
+def linear_triangulation(K, C1, R1, C2, R2, x1, x2):
+    """LinearTriangulation.py:95-99."""
+    return LinearTriangulation(K, C1, R1, C2, R2, x1, x2)
+
+
+# ---------------------------------------------------------------------------------------------
 # NonLinearTriangulation.py
 # ---------------------------------------------------------------------------------------------
 def Loss(X, x1, x2, P1, P2):

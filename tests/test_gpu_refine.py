@@ -125,3 +125,19 @@ def test_pnp_ransac_golden(cuda_device, tag):
     assert rel_err(C, g[f"Cransac_{tag}"]) < 1e-6 and rel_err(R, g[f"Rransac_{tag}"]) < 1e-6
     with pytest.raises(ValueError):
         pnp_ransac.PnPRANSAC(X[:3], x[:3], K)
+
+
+def test_lintri_golden_and_dropin(cuda_device):
+    """N1: batched DLT triangulation against the reference's own LinearTriangulation output."""
+    from sfm_b200 import refine
+    g = golden("nltri.npz")
+    X = refine.LinearTriangulation(g["K"], g["C1"], g["R1"], g["C2"], g["R2"], g["x1"], g["x2"])
+    assert X.shape == g["x0"].shape
+    err = np.linalg.norm(X - g["x0"], axis=1) / np.linalg.norm(g["x0"], axis=1)
+    assert err.max() < 1e-9, err.max()
+    X2 = refine.linear_triangulation(g["K"], g["C1"], g["R1"], g["C2"], g["R2"], g["x1"], g["x2"])
+    assert np.array_equal(X, X2)
+    assert refine.LinearTriangulation(g["K"], g["C1"], g["R1"], g["C2"], g["R2"], [], []).size == 0
+    # the pipeline composition the wrapper uses (Wrapper_dev.py:179,187): x0 -> non-linear refinement
+    Xr = refine.NonLinearTriangulation(g["K"], g["C1"], g["R1"], g["C2"], g["R2"], g["x1"], g["x2"], X)
+    assert rel_err(Xr, g["X"]) < 1e-6

@@ -92,3 +92,30 @@ def test_nlpnp_matches_reference(tag):
     assert rel_err(Cn, g[f"C_{tag}"]) < 1e-6 and rel_err(Rn, g[f"R_{tag}"]) < 1e-6
     cref = 0.5 * np.sum(so.pnp_loss(so.pose_to_params(g[f"C_{tag}"], g[f"R_{tag}"]), X, x, K) ** 2)
     assert cost.value <= cref * (1 + 1e-6)
+
+
+def test_lintri_matches_reference_golden():
+    """N1: the DLT null vector by one-sided Jacobi equals the reference's LinearTriangulation
+    (LAPACK dgesdd) on the frozen reference output, x0 of tests/golden/nltri.npz."""
+    import ctypes as C
+    g = golden("nltri.npz")
+    K = g["K"]
+    P1 = np.ascontiguousarray(K @ np.hstack([g["R1"], -g["R1"] @ g["C1"].reshape(3, 1)]))
+    P2 = np.ascontiguousarray(K @ np.hstack([g["R2"], -g["R2"] @ g["C2"].reshape(3, 1)]))
+    x1, x2 = np.ascontiguousarray(g["x1"]), np.ascontiguousarray(g["x2"])
+    n = len(x1)
+    X = np.zeros((n, 3))
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    hostsim.load().hs_lintri(vp(P1), vp(P2), vp(x1), vp(x2), C.c_int(n), vp(X))
+    err = np.linalg.norm(X - g["x0"], axis=1) / np.linalg.norm(g["x0"], axis=1)
+    assert err.max() < 1e-9, err.max()
+    # and against the oracle restatement on fresh inputs, far and near points included
+    rng = np.random.default_rng(1)
+    Xw = np.stack([rng.uniform(-3, 3, 200), rng.uniform(-2, 2, 200), rng.uniform(2, 60, 200)], axis=1)
+    xa = (P1 @ np.hstack([Xw, np.ones((200, 1))]).T).T
+    xb = (P2 @ np.hstack([Xw, np.ones((200, 1))]).T).T
+    xa, xb = np.ascontiguousarray(xa[:, :2] / xa[:, 2:]), np.ascontiguousarray(xb[:, :2] / xb[:, 2:])
+    ref = so.linear_triangulation(K, g["C1"], g["R1"], g["C2"], g["R2"], xa, xb)
+    Y = np.zeros((200, 3))
+    hostsim.load().hs_lintri(vp(P1), vp(P2), vp(xa), vp(xb), C.c_int(200), vp(Y))
+    assert rel_err(Y, ref) < 1e-9 and rel_err(Y, Xw) < 1e-6

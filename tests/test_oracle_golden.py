@@ -95,3 +95,9 @@ def test_ba_matches_reference(tag):
     # rows that are not valid points come back untouched
     inval = g["valid"].flatten() != 1
     assert np.array_equal(world[inval], g["world"][inval])
+
+
+def test_linear_triangulation_matches_reference():
+    g = golden("nltri.npz")
+    X = so.linear_triangulation(g["K"], g["C1"], g["R1"], g["C2"], g["R2"], g["x1"], g["x2"])
+    assert np.max(np.abs(X - g["x0"])) < 1e-9
