@@ -677,7 +677,7 @@ static size_t ba_layout(BAPlan &pl, unsigned char *base, int nc, int np, int nob
     CARVE(Dc, double, D * 6 * nc);
     CARVE(Dp, double, D * 3 * np);
     CARVE(S, double, D * (pl.npad + BA_NB) * pl.ld);
-    CARVE(Linv, double, D * (pl.npad / BA_NB) * BA_NB * BA_NB);
+    CARVE(Linv, double, D * (pl.npad / BA_NB) * BA_NB * BA_NB + (size_t)(pl.npad / BA_NB + 1) * (pl.npad / BA_NB) + 64);  // + K11's block flags
     CARVE(dc, double, D * pl.npad);
     CARVE(costpart, double, D * (pl.grid_obs + 8));
     CARVE(updpart, double, D * 4 * (pl.grid_pts + 2));

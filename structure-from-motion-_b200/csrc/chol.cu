@@ -37,6 +37,8 @@ struct CholSmem {
     // phase 1 / small phase 2: three NB x NB block views L | B | C; large phase 2: panel stages
     double buf[2 * 2 * 2 * CH_NB * CH_LDS];   // two stages of two 96 x 48 panels
     double x[CH_NB];
+    short act[1024];      // phase 2: super-rows of the trailing matrix whose panel blocks are not all zero
+    int nact, nact_cols;
     int fail;
 };
 static_assert(2 * 2 * 2 * CH_NB * CH_LDS >= 3 * CH_NB * CH_LDS, "block views must fit");
@@ -66,98 +68,207 @@ __device__ __forceinline__ double rsqrt_full(double d) {
     return y;
 }
 
+// -1/d to full double precision: MUFU seed (about 20 bits) and one cubic correction,
+// r = -y0 (1 + e + e^2) with e = 1 - d y0: three dependent DFMAs after the MUFU.
+__device__ __forceinline__ double neg_rcp_full(double d) {
+    double y0;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(d));
+    const double e = fma(-d, y0, 1.0);
+    const double q = fma(e, e, e);
+    return fma(-y0, q, -y0);
+}
+
 // Cholesky factor L (first block view of sm.buf, lower, strict upper part zero) and L^-1 (second
-// view) of the NB x NB diagonal block at Ablk (row-major, leading dimension ld, lower triangle
-// read). Right-looking sweep with the block held in REGISTERS: thread (ty, tx) of the 16 x 16
-// layout owns the 3 x 3 entries (ty + 16a, tx + 16b) of A and of M (an identity that receives
-// the same eliminations and so becomes L^-1). Per column j: the unscaled column j of A and row j
-// of M were published to shared memory by their owners at the end of the previous step
-// (double-buffered, so ONE barrier per column); every thread derives 1/sqrt(d) itself, applies
-//     A[i][m] -= a_ij a_mj / d,   M[i][c] -= a_ij m_jc / d
-// to its 3 x 3 tiles without any predicate (entries that are already final or dead just collect
-// garbage that nothing reads), and the finished column of L / row of L^-1 are written out from the
-// published values. ~55 instructions per thread and column; the dependent chain is
-// barrier -> LDS -> rsqrt -> 2 DMUL -> DFMA -> STS (measured on B200: tools/ubench/lat.cu).
-// Sets sm.fail on a non-positive pivot.
+// view) of the NB x NB diagonal block at Ablk (row-major, leading dimension ld, lower triangle read).
+//
+// Sweep: right-looking, two columns per step, the block held in REGISTERS of six warps. The sweep is
+// one long dependent chain; tools/diag_bench.py shows its cost is that chain plus the time the block
+// barrier waits for the shared-memory stores issued before it (roughly 30 cycles per STS
+// instruction, and twice that for a 16-byte one), so a step crosses ONE barrier and issues four
+// 8-byte stores per publishing thread for TWO columns. Thread (ty, tx) owns rows 2ty, 2ty+1 and columns 6tx .. 6tx+5; a warp
+// holds eight consecutive rows and drops out once the sweep has passed them. For the column pair
+// (2p, 2p+1) the owners published, at the end of step p-1, both columns as updated through column
+// 2p-1 into P2[p][col][row]; every thread then derives by itself -1/d1, the multiplier
+// t = -a_{2p+1,2p}/d1, the second pivot d2 = a_{2p+1,2p+1} + t a_{2p+1,2p}, -1/d2, and the updated
+// second column, and applies the rank-2 update to its tile without predicates (entries that are
+// already final just collect garbage nothing reads). P2 keeps every published pair, so the scaled
+// factor is written by all threads after the sweep. Dependent chain per PAIR of columns:
+// barrier -> LDS -> rcp -> 2 DP ops -> rcp -> DMUL -> DFMA -> STS.
+//
+// Inverse: blocked, after the sweep, all threads: the three 16 x 16 diagonal blocks by column-wise
+// forward substitution in registers, then X10 = -X11 (L10 X00), X21 = -X22 (L21 X11),
+// X20 = -X22 (L20 X00 + L21 X10) as small dense products.
+// Sets sm.fail on a pivot that is not positive and finite (NaNs then fill the block; callers test
+// the flag). Uses the first four block views of sm.buf.
+template <int V = 0>
 __device__ void factor_diag_block(CholSmem &sm, const double *Ablk, size_t ld, unsigned long long *prof = nullptr) {
     const long long c0 = clock64();
     double *Lout = sm.buf, *Xout = sm.buf + CH_NB * CH_LDS;
-    double *pub = sm.buf + 2 * CH_NB * CH_LDS;    // [2][2][NB]: parity x {column of A, row of M}
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    double A[3][3], M[3][3];
+    double *P2 = sm.buf + 2 * CH_NB * CH_LDS;     // [NB/2 pairs][2 cols][NB rows]
+    double *sinv = sm.buf + 3 * CH_NB * CH_LDS;   // [NB] 1/sqrt(pivot)
+    double *st = sinv + CH_NB;                     // [NB/2] multiplier t of each pair
+    double *T = sinv + 2 * CH_NB;                  // 2 x 16 x 16 scratch for the inverse
+    constexpr int HP = CH_NB / 2, PROW = HP * 4;   // 24 pairs, 96 doubles per published pair
+    const bool sweeper = threadIdx.x < 192;
+    const int tx = threadIdx.x & 7, ty = threadIdx.x >> 3;      // sweepers: ty in [0, 24)
+    const int last_p = sweeper ? 4 * (int)(threadIdx.x >> 5) + 3 : -1;   // this warp's rows end at 8w+7
+    double A[2][6];
+    if (sweeper) {
 #pragma unroll
-    for (int a = 0; a < 3; ++a)
+        for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int b = 0; b < 3; ++b) {
-            const int r = ty + 16 * a, c = tx + 16 * b;
-            A[a][b] = (c <= r) ? Ablk[(size_t)r * ld + c] : 0.0;
-            M[a][b] = (c == r) ? 1.0 : 0.0;
+            for (int b = 0; b < 6; b += 2) {
+                const int r = 2 * ty + a, c = 6 * tx + b;
+                const double2 v = *reinterpret_cast<const double2 *>(&Ablk[(size_t)r * ld + c]);
+                A[a][b] = (c <= r) ? v.x : 0.0;
+                A[a][b + 1] = (c + 1 <= r) ? v.y : 0.0;
+            }
+        if (tx == 0) {                             // pair 0
+            P2[2 * ty] = A[0][0]; P2[2 * ty + 1] = A[1][0];
+            P2[CH_NB + 2 * ty] = A[0][1]; P2[CH_NB + 2 * ty + 1] = A[1][1];
         }
+    }
     for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
         int r = e / CH_NB, c = e - r * CH_NB;
-        Lout[r * CH_LDS + c] = 0.0;
         Xout[r * CH_LDS + c] = 0.0;
-    }
-    // publish column 0 of A and row 0 of M
-    if (tx == 0) {
-#pragma unroll
-        for (int a = 0; a < 3; ++a) pub[ty + 16 * a] = A[a][0];
-    }
-    if (ty == 0) {
-#pragma unroll
-        for (int b = 0; b < 3; ++b) pub[CH_NB + tx + 16 * b] = M[0][b];
     }
     __syncthreads();
     const long long c1 = clock64();
-    for (int j = 0; j < CH_NB; ++j) {
-        const double *colA = pub + (j & 1) * 2 * CH_NB, *rowM = colA + CH_NB;
-        const double d = colA[j];
-        const bool bad = !(d > 0.0) || !(d < 1.7e308);
-        const double inv = bad ? 1.0 : rsqrt_full(d);
-        const double inv2 = inv * inv;
-        double xi[3], ym[3], mj[3];
+    // software pipeline: a step applies its rank-2 update only to the two tile columns published
+    // next; the other four columns take it at the top of the following step, where those DFMAs
+    // fill the latency slots of the pivot chain instead of delaying this step's barrier
+    double pxs[4] = {0.0, 0.0, 0.0, 0.0}, py1[6], py2[6];
 #pragma unroll
-        for (int a = 0; a < 3; ++a) xi[a] = colA[ty + 16 * a];
+    for (int b = 0; b < 6; ++b) py1[b] = py2[b] = 0.0;
+    for (int p0 = 0; p0 < HP; p0 += 3) {
 #pragma unroll
-        for (int b = 0; b < 3; ++b) {
-            ym[b] = colA[tx + 16 * b];
-            mj[b] = rowM[tx + 16 * b];
-        }
-        // finished column j of L (rows >= j) and row j of L^-1 (columns <= j)
-        if (tx == (j & 15)) {
+        for (int u = 0; u < 3; ++u) {
+            const int p = p0 + u;
+            if (p <= last_p) {                     // warp-uniform: rows above 2p are finished
+                const double *col0 = P2 + p * PROW, *col1 = col0 + CH_NB;
+                const double2 dA = *reinterpret_cast<const double2 *>(col0 + 2 * p);   // d1, c
+                const double d2p = col1[2 * p + 1];
+                const double2 x1 = *reinterpret_cast<const double2 *>(col0 + 2 * ty);
+                const double2 x2p = *reinterpret_cast<const double2 *>(col1 + 2 * ty);
+                double y1[6], y2[6];
 #pragma unroll
-            for (int a = 0; a < 3; ++a)
-                if (ty + 16 * a >= j) Lout[(ty + 16 * a) * CH_LDS + j] = xi[a] * inv;
-        }
-        if (ty == (j & 15)) {
+                for (int b = 0; b < 6; b += 2) {
+                    const double2 ya = *reinterpret_cast<const double2 *>(col0 + 6 * tx + b);
+                    const double2 yb = *reinterpret_cast<const double2 *>(col1 + 6 * tx + b);
+                    y1[b] = ya.x; y1[b + 1] = ya.y;
+                    y2[b] = yb.x; y2[b + 1] = yb.y;
+                }
+                // deferred part of the previous step (its published columns were 2*(u%3), +1)
+                const int bp = 2 * (u % 3);
 #pragma unroll
-            for (int b = 0; b < 3; ++b)
-                if (tx + 16 * b <= j) Xout[j * CH_LDS + tx + 16 * b] = mj[b] * inv;
-        }
-        if (threadIdx.x == 0 && bad) sm.fail = 1;
+                for (int b = 0; b < 6; ++b) {
+                    if (b == bp || b == bp + 1) continue;
+                    A[0][b] = fma(pxs[2], py2[b], fma(pxs[0], py1[b], A[0][b]));
+                    A[1][b] = fma(pxs[3], py2[b], fma(pxs[1], py1[b], A[1][b]));
+                }
+                const double r1 = neg_rcp_full(dA.x);
+                const double t = dA.y * r1;
+                const double r2 = neg_rcp_full(fma(t, dA.y, d2p));
+                pxs[0] = x1.x * r1; pxs[1] = x1.y * r1;
+                pxs[2] = fma(x1.x, t, x2p.x) * r2; pxs[3] = fma(x1.y, t, x2p.y) * r2;
 #pragma unroll
-        for (int a = 0; a < 3; ++a) {
-            const double xs = xi[a] * inv2;
+                for (int b = 0; b < 6; ++b) { py1[b] = y1[b]; py2[b] = fma(y1[b], t, y2[b]); }
+                const int bn = 2 * ((u + 1) % 3);
 #pragma unroll
-            for (int b = 0; b < 3; ++b) {
-                A[a][b] = fma(-xs, ym[b], A[a][b]);
-                M[a][b] = fma(-xs, mj[b], M[a][b]);
+                for (int b = bn; b < bn + 2; ++b) {
+                    A[0][b] = fma(pxs[2], py2[b], fma(pxs[0], py1[b], A[0][b]));
+                    A[1][b] = fma(pxs[3], py2[b], fma(pxs[1], py1[b], A[1][b]));
+                }
+                if (V != 4 && tx == p0 / 3 + (u + 1) / 3) {     // 8-byte stores: STS.128 costs ~25 cycles more each
+                    volatile double *n0 = P2 + (p + 1) * PROW + 2 * ty;   // volatile: keeps ptxas from pairing them
+                    n0[0] = A[0][bn]; n0[1] = A[1][bn];
+                    n0[CH_NB] = A[0][bn + 1]; n0[CH_NB + 1] = A[1][bn + 1];
+                }
             }
+            if (V == 5) __syncwarp();
+            else __syncthreads();
         }
-        // publish column j+1 of A and row j+1 of M into the other buffer
-        const int jn = j + 1, bn = jn >> 4;
-        double *colN = pub + (jn & 1) * 2 * CH_NB, *rowN = colN + CH_NB;
-        if (tx == (jn & 15)) {
+    }
+    if (V == 5) __syncthreads();
+    // pivots -> 1/sqrt, multipliers; then L = published columns scaled (strict upper part zero)
+    if (threadIdx.x < HP) {
+        const int p = threadIdx.x;
+        const double *col0 = P2 + p * PROW;
+        const double d1 = col0[2 * p], c = col0[2 * p + 1];
+        const double t = c * neg_rcp_full(d1);
+        const double d2 = fma(t, c, col0[CH_NB + 2 * p + 1]);
+        const bool bad1 = !(d1 > 1e-290) || !(d1 < 1e290), bad2 = !(d2 > 1e-290) || !(d2 < 1e290);
+        sinv[2 * p] = bad1 ? 1.0 : rsqrt_full(d1);
+        sinv[2 * p + 1] = bad2 ? 1.0 : rsqrt_full(d2);
+        st[p] = t;
+        if (bad1 || bad2) sm.fail = 1;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
+        const int j = e / CH_NB, i = e - j * CH_NB, p = j >> 1;
+        const double *col0 = P2 + p * PROW;
+        const double v = (j & 1) ? fma(col0[i], st[p], col0[CH_NB + i]) : col0[i];
+        Lout[i * CH_LDS + j] = (j <= i) ? v * sinv[j] : 0.0;
+    }
+    __syncthreads();
+    const long long c2 = clock64();
+    // ---- inverse ----
+    // diagonal 16 x 16 blocks: thread (blk, c) builds column c of L_bb^-1 in registers
+    if (threadIdx.x < CH_NB) {
+        const int blk = threadIdx.x >> 4, c = threadIdx.x & 15, o = 16 * blk;
+        double x[16], acc[16];
 #pragma unroll
-            for (int a = 0; a < 3; ++a) colN[ty + 16 * a] = bn == 0 ? A[a][0] : (bn == 1 ? A[a][1] : A[a][2]);
+        for (int i = 0; i < 16; ++i) { x[i] = 0.0; acc[i] = (i == c) ? 1.0 : 0.0; }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            // x_i = (e_c - sum_{m<i} L[i][m] x_m)_i / L[i][i]; zero above the diagonal (i < c)
+            const double xv = (i >= c) ? acc[i] * sinv[o + i] : 0.0;
+            x[i] = xv;
+#pragma unroll
+            for (int r = i + 1; r < 16; ++r) acc[r] = fma(-Lout[(o + r) * CH_LDS + o + i], xv, acc[r]);
         }
-        if (ty == (jn & 15)) {
 #pragma unroll
-            for (int b = 0; b < 3; ++b) rowN[tx + 16 * b] = bn == 0 ? M[0][b] : (bn == 1 ? M[1][b] : M[2][b]);
+        for (int i = 0; i < 16; ++i) Xout[(o + i) * CH_LDS + o + c] = x[i];
+    }
+    __syncthreads();
+    {
+        const int r = threadIdx.x >> 4, c = threadIdx.x & 15;      // one output of a 16 x 16 product each
+        // T0 = L10 X00, T1 = L21 X11
+        double t0 = 0.0, t1 = 0.0;
+#pragma unroll
+        for (int m = 0; m < 16; ++m) {
+            t0 = fma(Lout[(16 + r) * CH_LDS + m], Xout[m * CH_LDS + c], t0);
+            t1 = fma(Lout[(32 + r) * CH_LDS + 16 + m], Xout[(16 + m) * CH_LDS + 16 + c], t1);
+        }
+        T[r * 16 + c] = t0;
+        T[256 + r * 16 + c] = t1;
+        __syncthreads();
+        // X10 = -X11 T0, X21 = -X22 T1
+        double u0 = 0.0, u1 = 0.0;
+#pragma unroll
+        for (int m = 0; m < 16; ++m) {
+            u0 = fma(Xout[(16 + r) * CH_LDS + 16 + m], T[m * 16 + c], u0);
+            u1 = fma(Xout[(32 + r) * CH_LDS + 32 + m], T[256 + m * 16 + c], u1);
         }
         __syncthreads();
+        Xout[(16 + r) * CH_LDS + c] = -u0;
+        Xout[(32 + r) * CH_LDS + 16 + c] = -u1;
+        __syncthreads();
+        // T0 = L20 X00 + L21 X10
+        double t2 = 0.0;
+#pragma unroll
+        for (int m = 0; m < 16; ++m) {
+            t2 = fma(Lout[(32 + r) * CH_LDS + m], Xout[m * CH_LDS + c], t2);
+            t2 = fma(Lout[(32 + r) * CH_LDS + 16 + m], Xout[(16 + m) * CH_LDS + c], t2);
+        }
+        T[r * 16 + c] = t2;
+        __syncthreads();
+        double u2 = 0.0;
+#pragma unroll
+        for (int m = 0; m < 16; ++m) u2 = fma(Xout[(32 + r) * CH_LDS + 32 + m], T[m * 16 + c], u2);
+        Xout[(32 + r) * CH_LDS + c] = -u2;
     }
-    const long long c2 = clock64();
+    __syncthreads();
     if (prof && threadIdx.x == 0) {          // diagnostic: SM cycles of the column sweep / whole factor
         prof[6] += (unsigned long long)(c2 - c1);
         prof[7] += (unsigned long long)(clock64() - c0);
@@ -233,13 +344,41 @@ __device__ __forceinline__ void issue_panel96(double *s, const double *A, size_t
 }
 
 struct SuperTiles {
-    int b0, nJ, tri, ntiles;
-    __device__ __forceinline__ void init(int k, int nb) {
-        b0 = (k + 1) >> 1;                       // first super-row/col (may start one block early)
+    int nJ, tri, ntiles;
+    const short *act;
+    // Builds (all threads of the CTA, identical result in every CTA) the ascending list of ACTIVE
+    // super-rows of the trailing matrix at panel k: pairs of block-rows 2s, 2s+1 of which at least
+    // one has a non-zero panel block L_ik. The first super-row (it holds the next diagonal block,
+    // whose owner factors it) and the right-hand-side block-row are always active.
+    __device__ __forceinline__ void init(CholSmem &sm, const unsigned char *nz, int k, int nb) {
+        const int b0 = (k + 1) >> 1;             // first super-row/col (may start one block early)
         const int nI = ((nb + 2) >> 1) - b0;     // super-rows covering block-rows .. nb (RHS)
-        nJ = ((nb + 1) >> 1) - b0;               // super-cols covering block-cols .. nb-1
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            int base = 0, cols = 0;
+            for (int s0 = 0; s0 < nI; s0 += 32) {
+                const int sidx = b0 + s0 + (int)threadIdx.x;
+                bool a = false;
+                if (s0 + (int)threadIdx.x < nI) {
+                    const int i0 = 2 * sidx, i1 = 2 * sidx + 1;
+                    a = (sidx == b0) || i0 == nb || i1 == nb;
+                    if (i0 > k && i0 < nb) a = a || nz[(size_t)i0 * nb + k];
+                    if (i1 > k && i1 < nb) a = a || nz[(size_t)i1 * nb + k];
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, a);
+                if (a) sm.act[base + __popc(m & ((1u << threadIdx.x) - 1u))] = (short)sidx;
+                const bool col_ok = 2 * sidx < nb;      // holds at least one real block column
+                cols += __popc(__ballot_sync(0xffffffffu, a && col_ok));
+                base += __popc(m);
+            }
+            if (threadIdx.x == 0) { sm.nact = base; sm.nact_cols = cols; }
+        }
+        __syncthreads();
+        act = sm.act;
+        const int c = sm.nact;
+        nJ = sm.nact_cols;                       // the column-capable ones come first (ascending order)
         tri = nJ * (nJ + 1) / 2;
-        ntiles = tri + (nI - nJ) * nJ;
+        ntiles = tri + (c - nJ) * nJ;
     }
     __device__ __forceinline__ void decode(int t, int &I, int &J) const {
         int Ip, Jp;
@@ -252,8 +391,8 @@ struct SuperTiles {
             Ip = nJ + (t - tri) / nJ;
             Jp = (t - tri) - (Ip - nJ) * nJ;
         }
-        I = b0 + Ip;
-        J = b0 + Jp;
+        I = act[Ip];
+        J = act[Jp];
     }
 };
 
@@ -274,11 +413,11 @@ __device__ __forceinline__ int st_next_tile(int t, int cta, int G) {
 }
 
 template <bool DMMA, class FactorFn>
-__device__ void supertile_phase(CholSmem &sm, double *A, size_t ld, int k, int nb, int cta, int G,
-                                FactorFn &factor_next) {
+__device__ void supertile_phase(CholSmem &sm, double *A, size_t ld, const unsigned char *nz, int k, int nb,
+                                int cta, int G, FactorFn &factor_next) {
     double *buf = sm.buf;
     SuperTiles st;
-    st.init(k, nb);
+    st.init(sm, nz, k, nb);
     const int kcol = k * CH_NB, lo = (k + 1) * CH_NB, row_lim = (nb + 1) * CH_NB, col_lim = nb * CH_NB;
     int t = st_first_tile(cta, G), I = 0, J = 0, stage = 0;
     __syncthreads();                              // the phase-1 views of buf are dead from here on
@@ -412,6 +551,11 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
     if (threadIdx.x == 0) sm.fail = 0;
     __syncthreads();
     double *const sL = sm.buf, *const sB = sm.buf + CH_NB * CH_LDS, *const sC = sm.buf + 2 * CH_NB * CH_LDS;
+    // block sparsity: nz[i * nb + k] = 1 when the solved panel block L_ik (i > k) has a non-zero entry.
+    // Reduced camera systems of large scenes are block-sparse (cameras that share no point give an
+    // exactly zero block, and fill-in shows up as real non-zeros); zero blocks skip the panel solve,
+    // the trailing tiles they would feed, and their back-substitution term.
+    unsigned char *const nz = reinterpret_cast<unsigned char *>(Linv_ws + (size_t)nb * CH_NB * CH_NB);
     // optional phase profile (CTA 0, thread 0; ns): [0] diag factor [1] panel solve [2] barrier 1
     // [3] trailing update [4] barrier 2 [5] back substitution
     const bool profiling = prof != nullptr && cta == 0 && threadIdx.x == 0;
@@ -452,8 +596,16 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
             }
             for (int i = k + 1 + cta; i <= nb; i += G) {
                 __syncthreads();
-                load_block(sC, A, ld, i * CH_NB, k * CH_NB);
-                __syncthreads();
+                int any = 0;
+                for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
+                    int r = e / CH_NB, c = e - r * CH_NB;
+                    const double v = A[(size_t)(i * CH_NB + r) * ld + k * CH_NB + c];
+                    sC[r * CH_LDS + c] = v;
+                    any |= !(v == 0.0);
+                }
+                any = __syncthreads_or(any);
+                if (threadIdx.x == 0) nz[(size_t)i * nb + k] = (unsigned char)(any != 0);
+                if (!any) continue;               // an exactly zero block stays zero
                 // X = A_ik L^-T : X[r][c] = sum_m A_ik[r][m] Linv[c][m]
                 block_xyT<0>(sC, sB, sL);
                 __syncthreads();
@@ -469,7 +621,7 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
         const int m = nb - 1 - k;                 // remaining diagonal blocks
         if (m >= CH_SUPER_MIN) {
             // 96 x 96 super-tiles over the trailing block rows k+1 .. nb, aligned to even block indices
-            supertile_phase<DMMA>(sm, A, ld, k, nb, cta, G, factor_and_commit);
+            supertile_phase<DMMA>(sm, A, ld, nz, k, nb, cta, G, factor_and_commit);
         } else if (m > 0) {
             // tiles: for j' in [0, m): i' in [j', m]  (i' == m is the RHS block-row)
             const int ntiles = m * (m + 1) / 2 + m;
@@ -569,6 +721,7 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
         // y_b -= L_kb^T x_k for b < k: (block, quarter of the rows) pairs round-robin over CTAs would
         // need atomics; instead each CTA takes whole column blocks, 4 row-quarters per thread group
         for (int b = cta; b < k; b += G) {
+            if (!nz[(size_t)k * nb + b]) continue;          // zero block: no contribution (CTA-uniform)
             const int c = threadIdx.x & 63, part = threadIdx.x >> 6;
             double s = 0.0;
             if (c < CH_NB)
@@ -590,10 +743,11 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
 }
 
 // diagnostic: cycles of the diagonal-block factor alone (one CTA)
+template <int V>
 __global__ void __launch_bounds__(CH_THREADS) chol_diag_bench_kernel(const double *A48, unsigned long long *out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     CholSmem &sm = *reinterpret_cast<CholSmem *>(smem_raw);
-    factor_diag_block(sm, A48, CH_NB, out);
+    factor_diag_block<V>(sm, A48, CH_NB, out);
 }
 
 static int g_chol_grid = 0;
@@ -665,6 +819,7 @@ extern "C" size_t sfm_chol_solve_workspace_bytes(int32_t n) {
     size_t npad = (size_t)ceil_div(n, CH_NB) * CH_NB;
     size_t bytes = (npad + CH_NB) * npad * sizeof(double);              // A
     bytes += (npad / CH_NB) * (size_t)CH_NB * CH_NB * sizeof(double);    // Linv
+    bytes += align_up((npad / CH_NB + 1) * (npad / CH_NB), 256);        // block non-zero flags
     bytes += npad * sizeof(double) + 256;                                // x, flag
     return bytes;
 }
@@ -678,7 +833,7 @@ static int chol_solve_impl(const double *d_S, const double *d_g, int32_t n, doub
     size_t ld = (size_t)npad;
     double *A = reinterpret_cast<double *>(d_ws);
     double *Linv = A + (size_t)(npad + CH_NB) * ld;
-    double *x = Linv + (size_t)(npad / CH_NB) * CH_NB * CH_NB;
+    double *x = Linv + (size_t)(npad / CH_NB) * CH_NB * CH_NB + align_up((size_t)(npad / CH_NB + 1) * (npad / CH_NB), 256) / sizeof(double);
     int *flag = reinterpret_cast<int *>(x + npad);
     SFM_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), st));
     chol_pack_kernel<<<sm_count() * 4, 256, 0, st>>>(d_S, d_g, n, npad, ld, A);
@@ -704,12 +859,15 @@ extern "C" int sfm_chol_solve_profiled(const double *d_S, const double *d_g, int
 }
 
 extern "C" int sfm_chol_diag_bench(const double *d_A48, int32_t variant, uint64_t *d_out8, void *stream) {
-    if (!d_A48 || !d_out8 || variant != 0) return SFM_E_INVALID;
+    if (!d_A48 || !d_out8 || variant < 0 || variant > 5) return SFM_E_INVALID;
     cudaStream_t st = as_stream(stream);
     if (chol_grid_size() <= 0) return SFM_E_CUDA;
-    SFM_CUDA_TRY(cudaFuncSetAttribute(chol_diag_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(CholSmem)));
-    chol_diag_bench_kernel<<<1, CH_THREADS, sizeof(CholSmem), st>>>(d_A48, reinterpret_cast<unsigned long long *>(d_out8));
+    void (*fn)(const double *, unsigned long long *) =
+        variant == 0 ? chol_diag_bench_kernel<0> : variant == 1 ? chol_diag_bench_kernel<1> :
+        variant == 2 ? chol_diag_bench_kernel<2> : variant == 3 ? chol_diag_bench_kernel<3> :
+        variant == 4 ? chol_diag_bench_kernel<4> : chol_diag_bench_kernel<5>;
+    SFM_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(CholSmem)));
+    fn<<<1, CH_THREADS, sizeof(CholSmem), st>>>(d_A48, reinterpret_cast<unsigned long long *>(d_out8));
     SFM_LAUNCH_CHECK();
     return SFM_OK;
 }

@@ -7,7 +7,7 @@ from sfm_b200 import _lib, device
 lib = _lib.load()
 A = torch.randn(48, 60, dtype=torch.float64, device="cuda")
 S = (A @ A.T + torch.eye(48, dtype=torch.float64, device="cuda")).contiguous()
-for v, name in [(0, "full")]:
+for v, name in [(0, "full"), (1, "no rsqrt"), (2, "no L stores"), (3, "bar over 128"), (4, "no publish"), (5, "syncwarp only")]:
     out = torch.zeros(8, dtype=torch.int64, device="cuda")
     for _ in range(3):
         out.zero_()
