@@ -42,7 +42,9 @@ int chol_solve_launch(double *A, size_t ld, int npad, double *d_Linv, double *d_
                       cudaStream_t st, unsigned long long *d_prof);
 constexpr int BA_NB = 48;                 // == CH_NB in chol.cu
 constexpr int BA_CHUNK = 2048;            // observations per camera-pass CTA
-constexpr size_t BA_SMEM_CAM_LIMIT = 200 * 1024;
+constexpr int K9P_WARP_SCRATCH = 9 * 33 + 18;   // doubles of shared memory per warp of K9p (T[9][33] + 34 ints, padded)
+constexpr size_t BA_SMEM_MAX = 232448 - 1024;      // opt-in dynamic shared memory per CTA minus the static part
+constexpr size_t BA_SMEM_CAM_LIMIT = BA_SMEM_MAX - 16 * sizeof(double) * K9P_WARP_SCRATCH;   // table + 512-thread scratch
 
 struct KParam { double k[9]; };
 
@@ -139,7 +141,7 @@ ba_point_pass_kernel(KParam K, const double *__restrict__ camlin, int nc, const 
                      const int32_t *__restrict__ pt_idx, const int32_t *__restrict__ pt_ptr, int nobs,
                      double *__restrict__ W, double *__restrict__ V, double *__restrict__ gp,
                      double *__restrict__ costpart) {
-    extern __shared__ double scam[];
+    extern __shared__ __align__(16) double scam[];
     __shared__ double sred[32];
     const double *ctab = camlin;
     if (SMEM_CAMS) {
@@ -148,20 +150,37 @@ ba_point_pass_kernel(KParam K, const double *__restrict__ camlin, int nc, const 
         ctab = scam;
     }
     const int lane = threadIdx.x & 31;
+    // per-warp scratch of the segmented sum, behind the camera table: T[9][33] and the segment starts
+    double *sT = scam + (SMEM_CAMS ? (size_t)nc * CAMLIN_STRIDE : 0) + (size_t)(threadIdx.x >> 5) * K9P_WARP_SCRATCH;
+    int *sSeg = reinterpret_cast<int *>(sT + 9 * 33);
     double cost = 0.0;
     const int stride = gridDim.x * THREADS;
     const int nround = (nobs + 31) & ~31;
-    for (int o = blockIdx.x * THREADS + threadIdx.x; o < nround; o += stride) {
+    // software pipeline: the pass is latency bound (one wide CTA per SM when the camera table fills
+    // shared memory), so the index / observation loads run two iterations ahead and the point gather,
+    // whose address they produce, one iteration ahead of the arithmetic that consumes them
+    int o = blockIdx.x * THREADS + threadIdx.x;
+    int c_cur = 0, p_cur = -1, c_nx = 0, p_nx = -1;
+    double2 ob_cur = make_double2(0.0, 0.0), ob_nx = ob_cur;
+    double X[3] = {0.0, 0.0, 0.0};
+    if (o < nobs) { c_cur = cam_idx[o]; p_cur = pt_idx[o]; ob_cur = obs[o]; }
+    if (o + stride < nobs) { c_nx = cam_idx[o + stride]; p_nx = pt_idx[o + stride]; ob_nx = obs[o + stride]; }
+    if (p_cur >= 0) { X[0] = pts[3 * (size_t)p_cur]; X[1] = pts[3 * (size_t)p_cur + 1]; X[2] = pts[3 * (size_t)p_cur + 2]; }
+    for (; o < nround; o += stride) {
         const bool active = o < nobs;
-        int p = -1;
+        const long long o2 = (long long)o + 2LL * stride;
+        int c_n2 = 0, p_n2 = -1;
+        double2 ob_n2 = make_double2(0.0, 0.0);
+        if (o2 < nobs) { c_n2 = cam_idx[o2]; p_n2 = pt_idx[o2]; ob_n2 = obs[o2]; }
+        double Xn[3] = {0.0, 0.0, 0.0};
+        if (p_nx >= 0) { Xn[0] = pts[3 * (size_t)p_nx]; Xn[1] = pts[3 * (size_t)p_nx + 1]; Xn[2] = pts[3 * (size_t)p_nx + 2]; }
+        const int p = active ? p_cur : -1;
         double v[9];
 #pragma unroll
         for (int i = 0; i < 9; ++i) v[i] = 0.0;
         if (active) {
-            const int c = cam_idx[o];
-            p = pt_idx[o];
-            const double2 ob = obs[o];
-            double X[3] = {pts[3 * (size_t)p], pts[3 * (size_t)p + 1], pts[3 * (size_t)p + 2]};
+            const int c = c_cur;
+            const double2 ob = ob_cur;
             CamLin cl;
             camlin_load(ctab + (size_t)CAMLIN_STRIDE * c, cl);
             double ru, rv, jc[2][6], jp[2][3];
@@ -182,23 +201,38 @@ ba_point_pass_kernel(KParam K, const double *__restrict__ camlin, int nc, const 
             v[7] = jp[0][1] * ru + jp[1][1] * rv;
             v[8] = jp[0][2] * ru + jp[1][2] * rv;
         }
-        seg_reduce<9>(v, p, lane);
+        c_cur = c_nx; p_cur = p_nx; ob_cur = ob_nx;
+        c_nx = c_n2; p_nx = p_n2; ob_nx = ob_n2;
+        X[0] = Xn[0]; X[1] = Xn[1]; X[2] = Xn[2];
+        // Segmented sum of the nine per-observation values over the runs of equal point index in
+        // this warp. A shuffle scan moves 9 doubles through 5 levels (~200 SHFL per warp and pass:
+        // the MIO queue, not HBM, bounded the kernel); here every lane parks its values in shared
+        // memory and lane (s, k) of 3 x 9 sums quantity k of segment s, three segments per round.
         const int prev = __shfl_up_sync(0xffffffffu, p, 1);
         const bool head = (lane == 0) || (prev != p);
-        if (head && p >= 0) {
-            const int seg_beg = pt_ptr[p], seg_end = pt_ptr[p + 1];
-            const bool complete = (o == seg_beg) && (seg_end <= o - lane + 32);
-            double *Vp = V + 6 * (size_t)p, *gpp = gp + 3 * (size_t)p;
-            if (complete) {
+        const unsigned heads = __ballot_sync(0xffffffffu, head);
+        const int nseg = __popc(heads);
+        __syncwarp();                              // the previous pass has been read
 #pragma unroll
-                for (int i = 0; i < 6; ++i) Vp[i] = v[i];
-#pragma unroll
-                for (int i = 0; i < 3; ++i) gpp[i] = v[6 + i];
-            } else {
-#pragma unroll
-                for (int i = 0; i < 6; ++i) atomicAdd(Vp + i, v[i]);
-#pragma unroll
-                for (int i = 0; i < 3; ++i) atomicAdd(gpp + i, v[6 + i]);
+        for (int k = 0; k < 9; ++k) sT[k * 33 + lane] = v[k];
+        if (head) sSeg[__popc(heads & ((1u << lane) - 1u))] = lane;
+        if (lane == 0) sSeg[nseg] = 32;
+        __syncwarp();
+        const int sl = lane / 9, k9 = lane - 9 * sl;
+        for (int s0 = 0; s0 < nseg; s0 += 3) {
+            const int sg = s0 + sl;
+            const bool mine = lane < 27 && sg < nseg;
+            const int j0 = mine ? sSeg[sg] : 0, j1 = mine ? sSeg[sg + 1] : 0;
+            const int ps = __shfl_sync(0xffffffffu, p, j0);
+            if (mine && ps >= 0) {
+                double acc = 0.0;
+                for (int j = j0; j < j1; ++j) acc += sT[k9 * 33 + j];
+                const int seg_beg = pt_ptr[ps], seg_end = pt_ptr[ps + 1];
+                const int ow = o - lane;           // first observation of this warp's pass
+                const bool complete = (ow + j0 == seg_beg) && (seg_end <= ow + 32);
+                double *dst = k9 < 6 ? V + 6 * (size_t)ps + k9 : gp + 3 * (size_t)ps + (k9 - 6);
+                if (complete) *dst = acc;
+                else atomicAdd(dst, acc);
             }
         }
     }
@@ -213,7 +247,7 @@ ba_cost_kernel(const double *__restrict__ camlin, int nc, const double *__restri
                const double2 *__restrict__ obs, const int32_t *__restrict__ cam_idx,
                const int32_t *__restrict__ pt_idx, int nobs, double *__restrict__ costpart,
                double2 *__restrict__ r_out) {
-    extern __shared__ double scam[];
+    extern __shared__ __align__(16) double scam[];
     __shared__ double sred[32];
     const double *ctab = camlin;
     if (SMEM_CAMS) {
@@ -235,10 +269,8 @@ ba_cost_kernel(const double *__restrict__ camlin, int nc, const double *__restri
         double X2[3] = {pts[3 * (size_t)p2], pts[3 * (size_t)p2 + 1], pts[3 * (size_t)p2 + 2]};
         CamLin cl, cl2;
         const double *cp = ctab + (size_t)CAMLIN_STRIDE * c, *cp2 = ctab + (size_t)CAMLIN_STRIDE * c2;
-#pragma unroll
-        for (int i = 0; i < 9; ++i) { cl.M[i] = cp[i]; cl2.M[i] = cp2[i]; }
-#pragma unroll
-        for (int i = 0; i < 3; ++i) { cl.kt[i] = cp[9 + i]; cl2.kt[i] = cp2[9 + i]; }
+        camlin_load_proj(cp, cl);
+        camlin_load_proj(cp2, cl2);
         double ru, rv, ru2, rv2;
         ba_residual_only(cl, X, ob.x, ob.y, ru, rv);
         ba_residual_only(cl2, X2, ob2.x, ob2.y, ru2, rv2);
@@ -255,7 +287,7 @@ ba_cost_kernel(const double *__restrict__ camlin, int nc, const double *__restri
 
 // K9c. One CTA per (camera, chunk of its observations) in camera-major order.
 constexpr int K9C_THREADS = 128;
-__global__ void __launch_bounds__(K9C_THREADS, 4)
+__global__ void __launch_bounds__(K9C_THREADS, 3)
 ba_camera_pass_kernel(KParam K, const double *__restrict__ camlin, const double *__restrict__ pts,
                       const double2 *__restrict__ obs_c, const int32_t *__restrict__ pt_c,
                       const int32_t *__restrict__ chunk_cam, const int32_t *__restrict__ chunk_beg,
@@ -268,12 +300,28 @@ ba_camera_pass_kernel(KParam K, const double *__restrict__ camlin, const double 
     double acc[27];
 #pragma unroll
     for (int i = 0; i < 27; ++i) acc[i] = 0.0;
-    for (int o = beg + threadIdx.x; o < end; o += K9C_THREADS) {
-        const int p = pt_c[o];
-        const double2 ob = obs_c[o];
-        double X[3] = {pts[3 * (size_t)p], pts[3 * (size_t)p + 1], pts[3 * (size_t)p + 2]};
+    // software pipeline (as in K9p): index / observation two iterations ahead, point gather one ahead
+    int o = beg + threadIdx.x;
+    int p_nx = -1;
+    double2 ob_cur = make_double2(0.0, 0.0), ob_nx = ob_cur;
+    double X[3] = {0.0, 0.0, 0.0};
+    if (o < end) {
+        const int p0 = pt_c[o];
+        ob_cur = obs_c[o];
+        X[0] = pts[3 * (size_t)p0]; X[1] = pts[3 * (size_t)p0 + 1]; X[2] = pts[3 * (size_t)p0 + 2];
+    }
+    if (o + K9C_THREADS < end) { p_nx = pt_c[o + K9C_THREADS]; ob_nx = obs_c[o + K9C_THREADS]; }
+    for (; o < end; o += K9C_THREADS) {
+        int p_n2 = -1;
+        double2 ob_n2 = make_double2(0.0, 0.0);
+        if (o + 2 * K9C_THREADS < end) { p_n2 = pt_c[o + 2 * K9C_THREADS]; ob_n2 = obs_c[o + 2 * K9C_THREADS]; }
+        double Xn[3] = {0.0, 0.0, 0.0};
+        if (p_nx >= 0) { Xn[0] = pts[3 * (size_t)p_nx]; Xn[1] = pts[3 * (size_t)p_nx + 1]; Xn[2] = pts[3 * (size_t)p_nx + 2]; }
+        const double2 ob = ob_cur;
         double ru, rv, jc[2][6], jp[2][3];
         reproj_residual(cl, K.k, X, ob.x, ob.y, BA_EPS, ru, rv, jc, jp);
+        ob_cur = ob_nx; ob_nx = ob_n2; p_nx = p_n2;
+        X[0] = Xn[0]; X[1] = Xn[1]; X[2] = Xn[2];
 #pragma unroll
         for (int r = 0; r < 6; ++r) {
             acc[21 + r] += jc[0][r] * ru + jc[1][r] * rv;
@@ -485,6 +533,228 @@ ba_schur_kernel(const double *__restrict__ W, int nobs, const int32_t *__restric
     }
 }
 
+// K10a: thread per point -- MINPACK scale D_p (running maximum of the column norms), damped
+// V + lambda D_p^2, its inverse and b_p = V^-1 g_p; the gtol numerator max |g_j| / |J_j|.
+__global__ void __launch_bounds__(256)
+ba_point_prep_kernel(const double *__restrict__ V, const double *__restrict__ gp, double *__restrict__ Dp, int npts,
+                     double lambda, int update_D, int first, double *__restrict__ Vinv, double *__restrict__ bp,
+                     unsigned long long *__restrict__ gmax, int *__restrict__ fail) {
+    const int p = blockIdx.x * 256 + threadIdx.x;
+    double gm = 0.0;
+    if (p < npts) {
+        double v[6], g[3], d[3];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) v[i] = V[6 * (size_t)p + i];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) g[i] = gp[3 * (size_t)p + i];
+        if (update_D) {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                double cn = sqrt(v[sym_idx(j, j)]);
+                d[j] = first ? (cn == 0.0 ? 1.0 : cn) : fmax(Dp[3 * (size_t)p + j], cn);
+                if (cn > 0.0) gm = fmax(gm, fabs(g[j]) / cn);
+                Dp[3 * (size_t)p + j] = d[j];
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) d[j] = Dp[3 * (size_t)p + j];
+        }
+        v[0] += lambda * d[0] * d[0];
+        v[2] += lambda * d[1] * d[1];
+        v[5] += lambda * d[2] * d[2];
+        double vi[6], b[3];
+        if (!spd3_inverse(v, vi)) {
+            atomicOr(fail, 2);
+#pragma unroll
+            for (int i = 0; i < 6; ++i) vi[i] = 0.0;
+        }
+        sym3_mul(vi, g, b);
+#pragma unroll
+        for (int i = 0; i < 6; ++i) Vinv[6 * (size_t)p + i] = vi[i];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) bp[3 * (size_t)p + i] = b[i];
+    }
+    if (update_D) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) gm = fmax(gm, __shfl_xor_sync(0xffffffffu, gm, o));
+        if ((threadIdx.x & 31) == 0) atomic_max_pos(gmax, gm);
+    }
+}
+
+// K10b: the Schur complement by block ROW. The L2's FP64 atomic adders top out near 280 G adds/s
+// on B200 (tools/ubench/bulkred.cu: the same for scalar RED and for TMA bulk reductions), and a
+// point-major kernel needs 36 of them per camera pair of every point. Here a warp owns a slice
+// (<= 256 observations) of ONE camera's observation list (the camera-major index K9c already
+// uses) and accumulates that camera's block row S[ci, cj <= ci] in its own shared-memory window
+// of WB blocks, without atomics: for observation o of point p it forms Y_o = W_o V_p^-1 once and
+// adds -Y_o W_o'^T for the other observations o' of p, five at a time (lane = (o', column q)).
+// The window ends at the diagonal (cj in (ci - WB, ci]); cameras further down are collected in a
+// bit mask on the first pass and handled by further passes over the slice, so banded systems (large
+// scenes) take one pass and small dense ones at most ceil(nc / WB). A window is flushed with one
+// atomic per entry of each touched block: 36 per (slice, block) instead of 36 per (point, pair).
+// Also accumulates the right-hand side g_red[ci] -= W_o b_p.
+constexpr int SR_WARPS = 8;
+constexpr int SR_WB_MAX = 64;
+
+// everything one observation needs from global memory, fetched one observation ahead
+struct SrLoad {
+    int o0, L;
+    double a0, a1, a2, b0, b1, b2;     // lanes < 18: W_o[r][:], Vinv[:][k]; lanes 18..23: W_o[r][:], b_p
+    int cj[2];                         // the first two batches of the track (positions g and 5 + g)
+    double w[2][3];
+};
+
+__global__ void __launch_bounds__(SR_WARPS * 32, 2)
+ba_schur_rows_kernel(const double *__restrict__ W, int nobs, const int32_t *__restrict__ cam_idx,
+                     const int32_t *__restrict__ pt_ptr, const int32_t *__restrict__ perm,
+                     const int32_t *__restrict__ pt_c, const int32_t *__restrict__ chunk_cam,
+                     const int32_t *__restrict__ chunk_beg, const int32_t *__restrict__ chunk_end,
+                     const double *__restrict__ Vinv, const double *__restrict__ bp, int WB, int slice,
+                     double *__restrict__ S, size_t ld, double *__restrict__ gred) {
+    extern __shared__ __align__(16) double sr_smem[];
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int stride = WB * 36 + 24;
+    double *acc = sr_smem + (size_t)warp * stride, *Ys = acc + WB * 36;
+    const int ch = blockIdx.x, ci = chunk_cam[ch];
+    const int beg = chunk_beg[ch] + (blockIdx.y * SR_WARPS + warp) * slice, end = min(chunk_end[ch], beg + slice);
+    if (beg >= end) return;                        // (no block-wide barrier below)
+    const int g = lane / 6, q = lane - 6 * g;      // batch slot (g == 5: lanes 30, 31 idle) and block column
+    unsigned todo = 0;                             // windows below the first one that hold blocks of this row
+    double gacc = 0.0;                             // lanes 18..23: row ci of g_red
+    const int nwin = ci / WB + 1;
+    for (int d = 0; d < nwin; ++d) {
+        if (d > 0 && !((todo >> (d & 31)) & 1u)) continue;
+        const int w_hi = ci - d * WB, w0 = w_hi - WB + 1;     // window: cameras w0 .. w_hi (w0 may be negative)
+        for (int e = lane; e < WB * 36; e += 32) acc[e] = 0.0;
+        unsigned long long touched = 0ull;
+        __syncwarp();
+
+        // -Y W'^T of one batch into the window (cj < 0: no observation in this lane's slot)
+        auto batch = [&](const double (&Y)[18], int cj, double wq0, double wq1, double wq2) {
+            const bool lower = cj >= 0 && cj <= ci;
+            const bool inwin = lower && cj <= w_hi && cj >= w0;
+            if (d == 0 && lower && !inwin) todo |= 1u << (((ci - cj) / WB) & 31);
+            if (!__any_sync(full, inwin)) return;
+            // the same camera twice in one batch (it observed the point twice) would race
+            const unsigned same = __match_any_sync(full, inwin ? cj : -2 - lane);
+            const bool dup = __any_sync(full, inwin && __popc(same) > 6);
+            const int slot = cj - w0;
+            if (!dup) {
+                if (inwin) {
+                    double *a = acc + slot * 36 + q;
+#pragma unroll
+                    for (int r = 0; r < 6; ++r)
+                        a[6 * r] -= Y[3 * r] * wq0 + Y[3 * r + 1] * wq1 + Y[3 * r + 2] * wq2;
+                    touched |= 1ull << slot;
+                }
+            } else {
+                for (int gg = 0; gg < 5; ++gg) {
+                    if (inwin && g == gg) {
+                        double *a = acc + slot * 36 + q;
+#pragma unroll
+                        for (int r = 0; r < 6; ++r)
+                            a[6 * r] -= Y[3 * r] * wq0 + Y[3 * r + 1] * wq1 + Y[3 * r + 2] * wq2;
+                        touched |= 1ull << slot;
+                    }
+                    __syncwarp();
+                }
+            }
+        };
+
+        for (int kb = beg; kb < end; kb += 32) {
+            // lane-parallel index fetch for up to 32 observations of this camera
+            int o_l = 0, p_l = 0, o0_l = 0, L_l = 0;
+            if (kb + lane < end) {
+                o_l = perm[kb + lane];
+                p_l = pt_c[kb + lane];
+                o0_l = pt_ptr[p_l];
+                L_l = pt_ptr[p_l + 1] - o0_l;
+            }
+            const int cnt = min(32, end - kb);
+            auto fetch = [&](int i, SrLoad &f) {
+                const int o = __shfl_sync(full, o_l, i), p = __shfl_sync(full, p_l, i);
+                f.o0 = __shfl_sync(full, o0_l, i);
+                f.L = __shfl_sync(full, L_l, i);
+                f.a0 = f.a1 = f.a2 = f.b0 = f.b1 = f.b2 = 0.0;
+                if (lane < 24) {
+                    const int r = lane < 18 ? lane / 3 : lane - 18;
+                    f.a0 = W[(size_t)(3 * r) * nobs + o];
+                    f.a1 = W[(size_t)(3 * r + 1) * nobs + o];
+                    f.a2 = W[(size_t)(3 * r + 2) * nobs + o];
+                    if (lane < 18) {
+                        const int k = lane - 3 * r;
+                        const double *vi = Vinv + 6 * (size_t)p;
+                        f.b0 = vi[sym_idx(0, k)]; f.b1 = vi[sym_idx(1, k)]; f.b2 = vi[sym_idx(2, k)];
+                    } else {
+                        const double *b = bp + 3 * (size_t)p;
+                        f.b0 = b[0]; f.b1 = b[1]; f.b2 = b[2];
+                    }
+                }
+#pragma unroll
+                for (int bb = 0; bb < 2; ++bb) {
+                    const int t = 5 * bb + g;
+                    f.cj[bb] = -1;
+                    f.w[bb][0] = f.w[bb][1] = f.w[bb][2] = 0.0;
+                    if (g < 5 && t < f.L) {
+                        const size_t oo = (size_t)f.o0 + t;
+                        f.cj[bb] = cam_idx[oo];
+                        f.w[bb][0] = W[(size_t)(3 * q) * nobs + oo];
+                        f.w[bb][1] = W[(size_t)(3 * q + 1) * nobs + oo];
+                        f.w[bb][2] = W[(size_t)(3 * q + 2) * nobs + oo];
+                    }
+                }
+            };
+            SrLoad cur, nxt;
+            fetch(0, cur);
+            for (int i = 0; i < cnt; ++i) {
+                if (i + 1 < cnt) fetch(i + 1, nxt);
+                // lanes < 18: Y_o[r][k] = sum_m W_o[r][m] Vinv[m][k]; lanes 18..23: W_o[r][:] b_p
+                const double y = cur.a0 * cur.b0 + cur.a1 * cur.b1 + cur.a2 * cur.b2;
+                if (lane >= 18 && d == 0) gacc -= y;
+                __syncwarp();                      // the previous observation's Y has been read by every lane
+                if (lane < 18) Ys[lane] = y;
+                __syncwarp();
+                double Y[18];
+#pragma unroll
+                for (int e = 0; e < 18; ++e) Y[e] = Ys[e];
+                batch(Y, cur.cj[0], cur.w[0][0], cur.w[0][1], cur.w[0][2]);
+                if (cur.L > 5) batch(Y, cur.cj[1], cur.w[1][0], cur.w[1][1], cur.w[1][2]);
+                for (int t0 = 10; t0 < cur.L; t0 += 5) {          // long tracks: the rest in place
+                    const int t = t0 + g;
+                    int cj = -1;
+                    double wq0 = 0.0, wq1 = 0.0, wq2 = 0.0;
+                    if (g < 5 && t < cur.L) {
+                        const size_t oo = (size_t)cur.o0 + t;
+                        cj = cam_idx[oo];
+                        wq0 = W[(size_t)(3 * q) * nobs + oo];
+                        wq1 = W[(size_t)(3 * q + 1) * nobs + oo];
+                        wq2 = W[(size_t)(3 * q + 2) * nobs + oo];
+                    }
+                    batch(Y, cj, wq0, wq1, wq2);
+                }
+                cur = nxt;
+            }
+        }
+        __syncwarp();
+        if (d == 0) todo = __reduce_or_sync(full, todo);
+        unsigned t_lo = __reduce_or_sync(full, (unsigned)(touched & 0xffffffffull));
+        unsigned t_hi = __reduce_or_sync(full, (unsigned)(touched >> 32));
+        unsigned long long tm = ((unsigned long long)t_hi << 32) | t_lo;
+        while (tm) {
+            const int slot = __ffsll((long long)tm) - 1;
+            tm &= tm - 1;
+            const int cj = w0 + slot;
+            for (int e = lane; e < 36; e += 32) {
+                const int r = e / 6, qq = e - 6 * r;
+                atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * cj + qq], acc[slot * 36 + e]);
+            }
+        }
+        __syncwarp();
+    }
+    if (lane >= 18 && lane < 24) atomicAdd(&gred[6 * ci + lane - 18], gacc);
+}
+
 // ------------------------------------------------------------------------------ update (K12)
 // partial sums layout (4 doubles): [s.g, |D s|^2, |D x_new|^2, |D x_cur|^2]
 __global__ void __launch_bounds__(256)
@@ -597,6 +867,49 @@ ba_reduce_scalars_kernel(const double *__restrict__ costpart, int ncost, const d
 }
 
 // ------------------------------------------------------------------------------ host driver
+// development switches: SFM_SCHUR_ROWS=1 selects the block-row K10a/K10b pair instead of the
+// point-major K10 (measured on B200: rows 0.27 ms vs points 0.17 ms at C3, 3.35 vs 2.9 ms at C5 --
+// the row kernel issues ~280 instructions per observation and is latency bound at 16 warps per SM);
+// SFM_SCHUR_WB / SFM_SCHUR_SLICE override its window and slice.
+static bool schur_by_rows() {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("SFM_SCHUR_ROWS");
+        v = (e && e[0] == '1') ? 1 : 0;
+    }
+    return v == 1;
+}
+
+static int schur_window(int nc) {
+    static int forced = -1, attr_done = 0;
+    if (forced < 0) {
+        const char *e = getenv("SFM_SCHUR_WB");
+        forced = e ? std::max(1, std::min(SR_WB_MAX, atoi(e))) : 0;
+    }
+    if (!attr_done) {
+        cudaFuncSetAttribute(ba_schur_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(sizeof(double) * SR_WARPS * (SR_WB_MAX * 36 + 24)));
+        attr_done = 1;
+    }
+    if (forced) return forced;
+    return nc <= 48 ? nc : 40;       // 40 blocks per warp: two 8-warp CTAs per SM
+}
+
+// observations per warp of K10b: enough warps to fill the GPU several times over, few enough that the
+// window flushes (36 atomics per touched block and warp) stay small next to the accumulation
+static int schur_slice(int nobs) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char *e = getenv("SFM_SCHUR_SLICE");
+        forced = e ? std::max(1, std::min(BA_CHUNK / SR_WARPS, atoi(e))) : 0;
+    }
+    if (forced) return forced;
+    const int target_warps = sm_count() * 2 * SR_WARPS * 4;
+    int sl = 32;
+    while (sl < BA_CHUNK / SR_WARPS && nobs / sl > target_warps) sl *= 2;
+    return sl;
+}
+
 struct BAPlan {
     int nc, np, nobs, npad, nchunks, grid_obs, grid_pts, obs_threads;
     bool smem_cams;
@@ -639,8 +952,16 @@ static size_t ba_layout(BAPlan &pl, unsigned char *base, int nc, int np, int nob
     pl.cam_smem = (size_t)nc * CAMLIN_STRIDE * sizeof(double);
     pl.smem_cams = pl.cam_smem <= BA_SMEM_CAM_LIMIT;
     // a camera table above ~100 KB leaves room for one CTA per SM: make it a wide one (24 warps)
-    pl.obs_threads = (pl.smem_cams && pl.cam_smem > 100 * 1024) ? 768 : 256;
-    int per_sm = pl.obs_threads == 768 ? 1 : 2;
+    // a camera table above ~100 KB leaves room for one CTA per SM: make it as wide as the shared
+    // memory left for K9p's per-warp scratch allows
+    pl.obs_threads = 256;
+    if (pl.smem_cams && pl.cam_smem > 90 * 1024) {
+        const size_t room = BA_SMEM_MAX - pl.cam_smem, per_warp = sizeof(double) * K9P_WARP_SCRATCH;
+        pl.obs_threads = room >= 24 * per_warp ? 768 : room >= 20 * per_warp ? 640 : 512;
+        const char *e = getenv("SFM_K9P_THREADS");            // development switch: 512 / 640 / 768
+        if (e && (atoi(e) == 512 || atoi(e) == 640 || atoi(e) == 768) && atoi(e) <= pl.obs_threads) pl.obs_threads = atoi(e);
+    }
+    int per_sm = pl.obs_threads >= 512 ? 1 : 2;
     pl.grid_obs = std::max(1, std::min(sms * per_sm, ceil_div(nobs, pl.obs_threads)));
     pl.grid_pts = std::max(1, std::min(sms * 4, ceil_div(np, 256)));
     const int max_chunks = nobs / BA_CHUNK + nc + 1;
@@ -692,6 +1013,8 @@ template <bool SM>
 static void set_obs_kernel_attrs(size_t smem) {
     cudaFuncSetAttribute(ba_point_pass_kernel<SM, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(ba_point_pass_kernel<SM, 768, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(ba_point_pass_kernel<SM, 640, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(ba_point_pass_kernel<SM, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(ba_cost_kernel<SM, 256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(ba_cost_kernel<SM, 768, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 }
@@ -699,13 +1022,15 @@ static void set_obs_kernel_attrs(size_t smem) {
 static int launch_point_pass(const BAPlan &pl, const KParam &K, const double *camlin, const double *pts,
                              const double2 *obs, const int32_t *cam_idx, const int32_t *pt_idx, cudaStream_t st) {
     SFM_CUDA_TRY(cudaMemsetAsync(pl.V, 0, sizeof(double) * 9 * (size_t)pl.np, st));
-    const size_t sm = pl.smem_cams ? pl.cam_smem : 0;
+    const size_t sm = (pl.smem_cams ? pl.cam_smem : 0) + sizeof(double) * K9P_WARP_SCRATCH * (pl.obs_threads / 32);
 #define PP_ARGS K, camlin, pl.nc, pts, obs, cam_idx, pt_idx, pl.pt_ptr, pl.nobs, pl.W, pl.V, pl.gp, pl.costpart
     if (pl.smem_cams) {
         if (pl.obs_threads == 768) ba_point_pass_kernel<true, 768, 1><<<pl.grid_obs, 768, sm, st>>>(PP_ARGS);
+        else if (pl.obs_threads == 640) ba_point_pass_kernel<true, 640, 1><<<pl.grid_obs, 640, sm, st>>>(PP_ARGS);
+        else if (pl.obs_threads == 512) ba_point_pass_kernel<true, 512, 1><<<pl.grid_obs, 512, sm, st>>>(PP_ARGS);
         else ba_point_pass_kernel<true, 256, 2><<<pl.grid_obs, 256, sm, st>>>(PP_ARGS);
     } else {
-        ba_point_pass_kernel<false, 256, 2><<<pl.grid_obs, 256, 0, st>>>(PP_ARGS);
+        ba_point_pass_kernel<false, 256, 2><<<pl.grid_obs, 256, sm, st>>>(PP_ARGS);
     }
 #undef PP_ARGS
     SFM_LAUNCH_CHECK();
@@ -717,7 +1042,7 @@ static int launch_cost(const BAPlan &pl, const double *camlin, const double *pts
     const size_t sm = pl.smem_cams ? pl.cam_smem : 0;
 #define C_ARGS camlin, pl.nc, pts, obs, cam_idx, pt_idx, pl.nobs, pl.costpart, r_out
     if (pl.smem_cams) {
-        if (pl.obs_threads == 768) ba_cost_kernel<true, 768, 1><<<pl.grid_obs, 768, sm, st>>>(C_ARGS);
+        if (pl.obs_threads >= 512) ba_cost_kernel<true, 768, 1><<<pl.grid_obs, 768, sm, st>>>(C_ARGS);
         else ba_cost_kernel<true, 256, 2><<<pl.grid_obs, 256, sm, st>>>(C_ARGS);
     } else {
         ba_cost_kernel<false, 256, 2><<<pl.grid_obs, 256, 0, st>>>(C_ARGS);
@@ -846,7 +1171,7 @@ static int ba_prepare(BAPlan &pl, void *d_ws, size_t ws_bytes, int32_t n_cams, i
     size_t need = ba_layout(pl, base, n_cams, n_pts, n_obs);
     if ((size_t)(base - (unsigned char *)d_ws) + need > ws_bytes) return SFM_E_WORKSPACE;
     if (!g_attrs_set) {
-        set_obs_kernel_attrs<true>(BA_SMEM_CAM_LIMIT);
+        set_obs_kernel_attrs<true>(BA_SMEM_MAX);
         (void)cudaGetLastError();
         g_attrs_set = true;
     }
@@ -962,7 +1287,21 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
                                                                                            pl.ld, lambda, pl.S);
             SFM_LAUNCH_CHECK();
         }
-        {
+        if (schur_by_rows()) {
+            ba_point_prep_kernel<<<ceil_div(np, 256), 256, 0, st>>>(pl.V, pl.gp, pl.Dp, np, lambda, update_D, first_lin,
+                                                                   pl.Vinv, pl.bp, pl.gmax, pl.flags + 1);
+            SFM_LAUNCH_CHECK();
+            if (pl.nchunks) {
+                const int WB = schur_window(nc);
+                const size_t smem = sizeof(double) * SR_WARPS * ((size_t)WB * 36 + 24);
+                const int slice = schur_slice(nobs);
+                dim3 grid(pl.nchunks, ceil_div(BA_CHUNK, SR_WARPS * slice));
+                ba_schur_rows_kernel<<<grid, SR_WARPS * 32, smem, st>>>(
+                    pl.W, nobs, d_cam_idx, pl.pt_ptr, pl.perm, pl.pt_c, pl.chunk_cam, pl.chunk_beg, pl.chunk_end,
+                    pl.Vinv, pl.bp, WB, slice, pl.S, pl.ld, pl.S + (size_t)pl.npad * pl.ld);
+                SFM_LAUNCH_CHECK();
+            }
+        } else {
             int grid = std::max(1, std::min(sm_count() * 8, ceil_div(np, SCH_WARPS)));
             ba_schur_kernel<<<grid, SCH_WARPS * 32, 0, st>>>(pl.W, nobs, d_cam_idx, pl.pt_ptr, np, pl.V, pl.gp, pl.Dp,
                                                              lambda, update_D, first_lin, pl.Vinv, pl.bp, pl.S, pl.ld,

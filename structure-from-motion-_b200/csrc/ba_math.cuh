@@ -13,7 +13,10 @@
 namespace sfm {
 
 constexpr double BA_EPS = 1e-8;          // BundleAdjustment.py:38
-constexpr int CAMLIN_STRIDE = 21;        // doubles per linearised camera: M(9) kt(3) Jr(9)
+constexpr int CAMLIN_STRIDE = 22;        // doubles per linearised camera: M(9) kt(3) Jr(9) + 1 pad, so a
+                                         // record is 16-byte aligned and read with 11 128-bit loads: the
+                                         // per-lane gather of records from shared memory is bank-conflict
+                                         // bound, and wide loads halve its wavefronts
 
 SFM_HD void camlin_store(const CamLin &c, double *dst) {
 #pragma unroll
@@ -22,15 +25,48 @@ SFM_HD void camlin_store(const CamLin &c, double *dst) {
     for (int i = 0; i < 3; ++i) dst[9 + i] = c.kt[i];
 #pragma unroll
     for (int i = 0; i < 9; ++i) dst[12 + i] = c.Jr[i];
+    dst[21] = 0.0;
 }
 
 SFM_HD void camlin_load(const double *src, CamLin &c) {
+#ifdef __CUDA_ARCH__
+    double t[CAMLIN_STRIDE];
+    const double2 *s2 = reinterpret_cast<const double2 *>(src);
 #pragma unroll
-    for (int i = 0; i < 9; ++i) c.M[i] = src[i];
+    for (int i = 0; i < CAMLIN_STRIDE / 2; ++i) {
+        const double2 v = s2[i];
+        t[2 * i] = v.x;
+        t[2 * i + 1] = v.y;
+    }
+#else
+    const double *t = src;
+#endif
 #pragma unroll
-    for (int i = 0; i < 3; ++i) c.kt[i] = src[9 + i];
+    for (int i = 0; i < 9; ++i) c.M[i] = t[i];
 #pragma unroll
-    for (int i = 0; i < 9; ++i) c.Jr[i] = src[12 + i];
+    for (int i = 0; i < 3; ++i) c.kt[i] = t[9 + i];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) c.Jr[i] = t[12 + i];
+}
+
+// M and kt only (the residual-only pass)
+SFM_HD void camlin_load_proj(const double *src, CamLin &c) {
+#ifdef __CUDA_ARCH__
+    double t[12];
+    const double2 *s2 = reinterpret_cast<const double2 *>(src);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const double2 v = s2[i];
+        t[2 * i] = v.x;
+        t[2 * i + 1] = v.y;
+    }
+#else
+    const double *t = src;
+#endif
+#pragma unroll
+    for (int i = 0; i < 9; ++i) c.M[i] = t[i];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) c.kt[i] = t[9 + i];
 }
 
 // residual only (K8): no Jacobian work
