@@ -220,7 +220,11 @@ def run_ours(args, rank, world):
                         "correspondence set is SMEM/L2 resident, so the physical limiter is the FP64 pipe: "
                         "see fp64_pipe",
                 "fp64_pipe": {"fp64_instr_per_test": 31, "tests_per_launch": float(N_PTS) * N_HYP,
-                              "achieved_tinstr_s": 31.0 * N_PTS * N_HYP / (k2_ms * 1e-3) / 1e12}}
+                              "achieved_tinstr_s": 31.0 * N_PTS * N_HYP / (k2_ms * 1e-3) / 1e12,
+                              # one FP64 warp instruction per 2 cycles and scheduler (measured,
+                              # profiles/r01_ubench_b200.txt): 148 SMs x 4 x 16 lanes x 1.965 GHz
+                              "peak_tinstr_s": 148 * 4 * 16 * 1.965e9 / 1e12,
+                              "frac": 31.0 * N_PTS * N_HYP / (k2_ms * 1e-3) / (148 * 4 * 16 * 1.965e9)}}
 
     # end to end through the drop-in signature: host numpy in, host numpy out, RNG replay, H2D, D2H
     index = np.arange(N_PTS)

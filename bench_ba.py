@@ -171,7 +171,10 @@ def run_single_gpu(args, peaks, peak_src, flush):
                             "lm_iterations_per_solve": its5 / 3, "cost": infos5[-1]["cost"],
                             "rmse_px": float(np.sqrt(2 * infos5[-1]["cost"] / n5)), "passes": passes}
     out["roofline"] = {"bound": "hbm", "kernel": "ba_point_pass_kernel (K9p) on C5", "achieved": k9["achieved_gbs"],
-                       "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": k9["frac_of_measured_hbm"], "traffic": None,
+                       "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": k9["frac_of_measured_hbm"],
+                       # dram__bytes_read.sum + dram__bytes_write.sum of this kernel on this workload, one
+                       # ncu --set full capture (profiles/r01_k9p_c5_v3_ncu_details.txt): 110.3 + 552.4 MB
+                       "traffic": 662.7e6,
                        "peak_source": peak_src, "kernel_ms": k9["ms"], "algorithmic_bytes_per_launch": k9["algorithmic_bytes"],
                        "note": "168 B per observation + 168 B per point (DESIGN.md); timed alone with CUDA events, "
                                "includes the 36 MB memset of V/g_p and the per-camera linearisation reuse"}

@@ -112,6 +112,58 @@ def f_ransac_host(points1, points2, samples, threshold, want_err=False, want_all
     return out
 
 
+_PINNED: dict = {}
+STREAM_MIN_HYPOTHESES = 16384      # below this one sfm_f_ransac call is cheaper than chunking
+STREAM_CHUNKS = 8
+
+
+def _pinned_i32(rows: int, cols: int) -> torch.Tensor:
+    """Grow-only pinned staging buffer for the sample index sets."""
+    need = rows * cols
+    buf = _PINNED.get("samples")
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.int32, pin_memory=True)
+        _PINNED["samples"] = buf
+    return buf[:need].view(rows, cols)
+
+
+def f_ransac_stream(points1, points2, threshold, n_max, chunks=STREAM_CHUNKS):
+    """GetInliersRANSAC's hot loop with the host work overlapped: the reference's RNG stream is
+    replayed chunk by chunk into pinned memory while the GPU generates and scores the previous
+    chunk (K1 + K2 per chunk, one K3 over all counts, K4 with the winner's row of F). The draws, their order and every result are the
+    same as one sfm_f_ransac call over the whole stream. Returns the dict of f_ransac_host."""
+    lib, st = _lib.load(), None
+    x1x2 = np.ascontiguousarray(np.hstack([np.asarray(points1, np.float64), np.asarray(points2, np.float64)]))
+    n, h = len(x1x2), int(n_max)
+    d_x = device.to_device(x1x2)
+    st = device.stream()
+    r = _alloc_result(n, h, False)
+    key = device.empty((1,), torch.int64)
+    d_s = device.empty((h, 8), torch.int32)
+    pinned = _pinned_i32(h, 8)
+    host = pinned.numpy()
+    chunk = max(1, -(-h // max(1, int(chunks))))
+    for off in range(0, h, chunk):
+        c = min(chunk, h - off)
+        sampler.sample_stream(n, 8, c, out=host[off:off + c])
+        d_s[off:off + c].copy_(pinned[off:off + c], non_blocking=True)
+        _lib.check(lib.sfm_f8pt_batch(device.ptr(d_x), n, device.ptr(d_s) + 32 * off, c,
+                                      device.ptr(r.F) + 72 * off, st), "sfm_f8pt_batch")
+        _lib.check(lib.sfm_f_score_count(device.ptr(d_x), n, device.ptr(r.F) + 72 * off, c, float(threshold),
+                                         device.ptr(r.counts) + 4 * off, st), "sfm_f_score_count")
+    _lib.check(lib.sfm_argmax_first(device.ptr(r.counts), h, 0, device.ptr(r.best), device.ptr(key), st),
+               "sfm_argmax_first")
+    # F_best = F[winner] without a host round trip (a device-side row gather), then K4 with it
+    r.F_best.copy_(r.F.index_select(0, r.best[:1].long()).view(9))
+    _lib.check(lib.sfm_f_inlier_mask(device.ptr(d_x), n, device.ptr(r.F_best), float(threshold),
+                                     device.ptr(r.mask), 0, st), "sfm_f_inlier_mask")
+    packed = r.packed.cpu().numpy()            # synchronises the stream
+    return dict(F_best=packed[:72].view(np.float64).reshape(3, 3).copy(),
+                best_idx=int(packed[72:76].view(np.int32)[0]),
+                best_count=int(packed[76:80].view(np.int32)[0]),
+                mask=packed[80:].astype(bool))
+
+
 def GetInliersRANSAC(points1, points2, index, threshold=0.06, n_max=1000):
     """Drop-in for GetInliersRANSAC.py:5-106 -> (inlier_index, outlier_indices, F_best)."""
     points1 = np.array(points1)
@@ -120,13 +172,17 @@ def GetInliersRANSAC(points1, points2, index, threshold=0.06, n_max=1000):
     n_points = len(points1)
     if n_points < 8:                                   # GetInliersRANSAC.py:38-40 (no RNG draw)
         return np.array([]), index, None
-    samples = sampler.sample_stream(n_points, 8, int(n_max))   # one draw per iteration (:55)
-    if n_max <= 0:
-        return np.array([]), index, None
-    if points1.ndim != 2 or points1.shape[1] != 2 or points2.shape != points1.shape:
-        # EstimateFundamentalMatrix raises inside the try of every iteration (:59,:90-92)
-        return np.array([]), index, None
-    res = f_ransac_host(points1, points2, samples, threshold)
+    shape_ok = points1.ndim == 2 and points1.shape[1] == 2 and points2.shape == points1.shape
+    if shape_ok and int(n_max) >= STREAM_MIN_HYPOTHESES:
+        res = f_ransac_stream(points1, points2, threshold, int(n_max))
+    else:
+        samples = sampler.sample_stream(n_points, 8, int(n_max))   # one draw per iteration (:55)
+        if n_max <= 0:
+            return np.array([]), index, None
+        if not shape_ok:
+            # EstimateFundamentalMatrix raises inside the try of every iteration (:59,:90-92)
+            return np.array([]), index, None
+        res = f_ransac_host(points1, points2, samples, threshold)
     if res["best_count"] == 0:                         # :95-96
         return np.array([]), index, None
     mask = res["mask"]

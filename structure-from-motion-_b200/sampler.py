@@ -20,11 +20,14 @@ def _python_stream(n: int, k: int, count: int) -> np.ndarray:
     return out
 
 
-def sample_stream(n: int, k: int, count: int) -> np.ndarray:
-    """[count, min(k,n)] int32 index sets; advances the global `random` state like the reference."""
+def sample_stream(n: int, k: int, count: int, out: np.ndarray | None = None) -> np.ndarray:
+    """[count, min(k,n)] int32 index sets; advances the global `random` state like the reference.
+    `out` (optional): a C-contiguous int32 [count, min(k,n)] array to fill (e.g. pinned memory)."""
     k = min(k, n)
     if count <= 0 or k <= 0:
         return np.empty((max(count, 0), max(k, 0)), dtype=np.int32)
+    if out is not None and (out.shape != (count, k) or out.dtype != np.int32 or not out.flags.c_contiguous):
+        raise ValueError("out must be a C-contiguous int32 array of shape (count, min(k, n))")
     inst = getattr(random, "_inst", None)
     fast = (type(inst) is random.Random and getattr(random.sample, "__self__", None) is inst
             and n < 2 ** 31 and k <= 64 and count >= 16)
@@ -32,10 +35,15 @@ def sample_stream(n: int, k: int, count: int) -> np.ndarray:
         st = random.getstate()
         fast = st[0] == 3 and len(st[1]) == 625
     if not fast:
-        return _python_stream(n, k, count)
+        res = _python_stream(n, k, count)
+        if out is not None:
+            out[...] = res
+            return out
+        return res
     mt = np.array(st[1][:624], dtype=np.uint32)
     idx = C.c_int32(st[1][624])
-    out = np.empty((count, k), dtype=np.int32)
+    if out is None:
+        out = np.empty((count, k), dtype=np.int32)
     rc = _lib.load().sfm_mt_sample_stream(mt.ctypes.data, C.addressof(idx), n, k, count, out.ctypes.data)
     _lib.check(rc, "sfm_mt_sample_stream")
     random.setstate((3, tuple(int(v) for v in mt) + (int(idx.value),), st[2]))

@@ -152,3 +152,31 @@ def test_edge_cases(cuda_device):
     random.seed(2)
     so.draw_samples(20, 8, 30)
     assert len(inl) == 0 and F is None and after == random.random()
+
+
+def test_fransac_stream_equals_single_call(cuda_device):
+    """The chunk-pipelined host path (RNG replay overlapped with K1/K2) consumes the same draws and
+    returns the same winner, F and mask as one sfm_f_ransac call; the drop-in switches to it for
+    large n_max and leaves the global generator in the state the reference would."""
+    from sfm_b200 import scenes, sampler
+    ransac = _ransac()
+    sc = scenes.two_view(n=4000, seed=5)
+    x1, x2 = sc["x1"], sc["x2"]
+    h = 20_000
+    random.seed(777)
+    samples = sampler.sample_stream(len(x1), 8, h)
+    state_after = random.getstate()
+    ref = ransac.f_ransac_host(x1, x2, samples, 0.06)
+    for chunks in (1, 3, 8):
+        random.seed(777)
+        got = ransac.f_ransac_stream(x1, x2, 0.06, h, chunks=chunks)
+        assert random.getstate() == state_after
+        assert got["best_idx"] == ref["best_idx"] and got["best_count"] == ref["best_count"]
+        assert np.array_equal(got["F_best"], ref["F_best"])
+        assert np.array_equal(got["mask"], ref["mask"])
+    # through the drop-in signature
+    random.seed(777)
+    inl, outl, F = ransac.GetInliersRANSAC(x1, x2, np.arange(len(x1)), 0.06, h)
+    assert h >= ransac.STREAM_MIN_HYPOTHESES
+    assert np.array_equal(inl, np.where(ref["mask"])[0]) and np.array_equal(F, ref["F_best"])
+    assert random.getstate() == state_after
