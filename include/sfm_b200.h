@@ -244,6 +244,25 @@ int sfm_chol_diag_bench(const double *d_A48, int32_t variant, uint64_t *d_out8, 
 
 /* @@MORE@@ (further sections are appended above this marker as the path widens) */
 
+/* ---- N4: two-view pose front end ------------------------------------------------
+ * Replaces EssentialMatrixFromFundamentalMatrix.py:19, ExtractCameraPose.py:24-81, the four
+ * LinearTriangulation calls of Wrapper_dev.py:166-168 and DisambiguateCameraPose.py:53-92, so a pair
+ * stays on the device between F-RANSAC and NonLinearTriangulation.
+ *   d_F      [9]      fundamental matrix (device, e.g. d_Fbest of sfm_f_ransac);  h_K HOST 3x3
+ *   d_cfg48  [4,12]   (C[3], R[9]) in the reference's order (R1,t) (R1,-t) (R2,t) (R2,-t); the
+ *                     assignment of the list positions depends on the SVD sign convention (LAPACK's
+ *                     in the reference, documented in twoview.cu here): the SET is the same
+ *   d_P60    [5,12]   K[I|0] and K R_i [I | -C_i]
+ *   d_Xall   [4,n,3]  DLT points under each configuration;  d_counts4 [4] cheirality votes
+ *   d_best2  [2]      (index, votes) of the first maximum;  d_pose12 = its (C, R) */
+int sfm_two_view_configs(const double *d_F, const double *h_K, double *d_cfg48, double *d_P60,
+                         int32_t *d_counts4, void *stream);
+int sfm_cheirality_count(const double *d_cfg48, const double *d_Xall, int32_t n, int32_t *d_counts4,
+                         void *stream);
+int sfm_two_view_pose(const double *d_F, const double *h_K, const double *d_x1, const double *d_x2,
+                      int32_t n, double *d_cfg48, double *d_P60, double *d_Xall, int32_t *d_counts4,
+                      int32_t *d_best2, double *d_pose12, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -41,6 +41,9 @@ import NonLinearTriangulation as refNLT  # noqa: E402
 import NonlinearPnP as refNLP  # noqa: E402
 import PnPRANSAC as refPR  # noqa: E402
 import Utils as refUtils  # noqa: E402
+import EssentialMatrixFromFundamentalMatrix as refE  # noqa: E402
+import ExtractCameraPose as refECP  # noqa: E402
+import DisambiguateCameraPose as refDCP  # noqa: E402
 
 VERS = dict(numpy=np.__version__, scipy=scipy.__version__, python=sys.version.split()[0])
 
@@ -132,6 +135,25 @@ def gen_tri():
          x2=sc["x2"], x0=x0, X=X, x0b=x0b, Xb=Xb, loss0=loss0)
 
 
+def gen_twoview():
+    """Two-view pose front end: E from F, the four (C, R) configurations, their DLT
+    triangulations and the cheirality pick, on two seeded scenes (clean and with outliers)."""
+    out = {}
+    for tag, sc in (("a", scenes.two_view(n=400, outlier_frac=0.0, seed=31)),
+                    ("b", scenes.two_view(n=600, outlier_frac=0.2, seed=32))):
+        with redirect_stdout(io.StringIO()), np.errstate(all="ignore"):
+            F = refEFM.EstimateFundamentalMatrix(sc["x1"], sc["x2"])
+            E = refE.EssentialMatrixFromFundamentalMatrix(F, sc["K"])
+            Cset, Rset = refECP.ExtractCameraPose(E)
+            Xset = [refLT.LinearTriangulation(sc["K"], np.zeros(3), np.eye(3), c, r, sc["x1"], sc["x2"])
+                    for c, r in zip(Cset, Rset)]
+            C, R, X = refDCP.DisambiguateCameraPose(Cset, Rset, Xset)
+        out.update({f"K_{tag}": sc["K"], f"x1_{tag}": sc["x1"], f"x2_{tag}": sc["x2"], f"F_{tag}": F, f"E_{tag}": E,
+                    f"Cset_{tag}": Cset, f"Rset_{tag}": Rset, f"Xset_{tag}": np.array(Xset), f"C_{tag}": C,
+                    f"R_{tag}": R, f"X_{tag}": X})
+    save("twoview.npz", **out)
+
+
 def gen_pnp():
     out = {}
     for tag, n, ofrac, seed in (("a", 300, 0.0, 31), ("b", 2000, 0.10, 32), ("c", 12, 0.0, 33)):
@@ -212,6 +234,6 @@ def gen_ba():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["f8pt", "fransac", "p3data", "tri", "pnp", "ba"]
+    which = sys.argv[1:] or ["f8pt", "fransac", "p3data", "tri", "pnp", "ba", "twoview"]
     for w in which:
         globals()["gen_" + w]()

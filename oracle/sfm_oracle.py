@@ -306,3 +306,47 @@ def linear_triangulation(K, C1, R1, C2, R2, x1, x2):
         Xh = np.linalg.svd(A)[2][-1]                               # :84-85
         out.append(Xh[:3] / Xh[3] if abs(Xh[3]) > 1e-8 else Xh[:3])   # :88-92
     return np.array(out)
+
+
+# ------------------------------------------------------------------ two-view pose front end (N4)
+def essential_from_fundamental(F, K):
+    """EssentialMatrixFromFundamentalMatrix.py:19."""
+    return np.asarray(K).T @ np.asarray(F) @ np.asarray(K)
+
+
+def extract_camera_pose(E):
+    """ExtractCameraPose.py:24-81: four (C, R) configurations from numpy's SVD of E. The ORDER of the
+    list follows LAPACK's sign choice for the singular vectors; the set does not."""
+    U, _, Vt = np.linalg.svd(np.array(E))
+    if np.linalg.det(U) * np.linalg.det(Vt) < 0:
+        U[:, -1] *= -1
+    W = np.array([[0, -1, 0], [1, 0, 0], [0, 0, 1]])
+    R1, R2 = U @ W @ Vt, U @ W.T @ Vt
+    t = U[:, 2] / np.linalg.norm(U[:, 2])
+    Cset = np.array([-R1.T @ t, -R1.T @ (-t), -R2.T @ t, -R2.T @ (-t)])
+    Rset = np.array([R1, R1, R2, R2])
+    return Cset, Rset
+
+
+def cheirality_counts(Cset, Rset, Xset):
+    """DisambiguateCameraPose.py:66-76: points with positive depth in both cameras, per configuration."""
+    out = []
+    for C, R, X in zip(Cset, Rset, Xset):
+        X = np.asarray(X).reshape(-1, 3)
+        z2 = ((R @ (X - np.asarray(C).reshape(1, 3)).T).T)[:, 2] if len(X) else np.zeros(0)
+        out.append(int(np.sum((X[:, 2] > 0) & (z2 > 0))) if len(X) else 0)
+    return np.array(out)
+
+
+def disambiguate_camera_pose(Cset, Rset, Xset):
+    """DisambiguateCameraPose.py:53-92: first maximum of the vote (strict '>' from -1, empty sets skipped)."""
+    counts = cheirality_counts(Cset, Rset, Xset)
+    best, best_count = None, -1
+    for i in range(len(Cset)):
+        if len(Xset[i]) == 0:
+            continue
+        if counts[i] > best_count:
+            best, best_count = i, counts[i]
+    if best is None:
+        return np.asarray(Cset[0]), np.asarray(Rset[0]), np.asarray(Xset[0]), 0, -1
+    return np.array(Cset[best]), np.array(Rset[best]), np.array(Xset[best]), best, int(best_count)

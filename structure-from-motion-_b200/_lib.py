@@ -37,6 +37,10 @@ SIGNATURES = {
     "sfm_nltri": (C.c_int, [c_vp, c_vp, c_f64p, c_f64p, c_f64p, C.c_int32, C.c_int32, C.c_double,
                             c_f64p, c_f64p, c_i32p, c_vp]),
     "sfm_lintri": (C.c_int, [c_vp, c_vp, c_f64p, c_f64p, C.c_int32, c_f64p, c_vp]),
+    "sfm_two_view_configs": (C.c_int, [c_f64p, c_vp, c_f64p, c_f64p, c_i32p, c_vp]),
+    "sfm_cheirality_count": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_i32p, c_vp]),
+    "sfm_two_view_pose": (C.c_int, [c_f64p, c_vp, c_f64p, c_f64p, C.c_int32, c_f64p, c_f64p, c_f64p,
+                                    c_i32p, c_i32p, c_f64p, c_vp]),
     "sfm_pnp_score_count": (C.c_int, [c_f64p, c_f64p, c_f64p, C.c_int32, C.c_int32, C.c_double,
                                       c_i32p, c_vp]),
     "sfm_nlpnp_batch": (C.c_int, [c_vp, c_f64p, c_f64p, c_i32p, C.c_int32, c_f64p, C.c_int32,

@@ -1,0 +1,9 @@
+"""Drop-in replacement for the reference module of the same name (Wrapper_dev.py:8-9, DisambiguateCameraPose.py:3).
+Put this directory ahead of the reference's `Phase 1/` on sys.path; exports the same name as ExtractCameraPose.py:3."""
+import os as _os
+import sys as _sys
+
+_sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__)))))
+from sfm_b200.two_view import ExtractCameraPose  # noqa: E402,F401
+
+_sys.path.pop(0)
