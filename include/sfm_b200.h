@@ -263,6 +263,26 @@ int sfm_two_view_pose(const double *d_F, const double *h_K, const double *d_x1, 
                       int32_t n, double *d_cfg48, double *d_P60, double *d_Xall, int32_t *d_counts4,
                       int32_t *d_best2, double *d_pose12, void *stream);
 
+/* ---- N2: homography RANSAC ----------------------------------------------------------
+ * Replaces GetHomographyInliers.py: find_homography :4-82 and the RANSAC loop :85-165, on the K1..K4
+ * skeleton. d_x1x2 [n,4] rows (x1,y1,x2,y2); d_sample [h,4] from the reference's random.sample
+ * stream (:126); threshold in pixels (strict '<' on the reprojection distance, :149). */
+int sfm_h4pt_batch(const double *d_x1x2, int32_t n, const int32_t *d_sample, int32_t h, double *d_H,
+                   void *stream);
+int sfm_h_score_count(const double *d_x1x2, int32_t n, const double *d_H, int32_t h, double threshold,
+                      int32_t *d_counts, void *stream);
+int sfm_h_inlier_mask(const double *d_x1x2, int32_t n, const double *d_Hone, double threshold,
+                      uint8_t *d_mask, double *d_err, void *stream);
+/* K1..K4 chained; outputs as sfm_f_ransac: d_H [h,9], d_counts [h], d_best [2], d_Hbest [9],
+ * d_mask [n] (all zero when the best count is 0), d_err [n] (may be null). */
+int sfm_h_ransac(const double *d_x1x2, int32_t n, const int32_t *d_sample, int32_t h, double threshold,
+                 double *d_H, int32_t *d_counts, int32_t *d_best, double *d_Hbest, uint8_t *d_mask,
+                 double *d_err, void *stream);
+/* find_homography for ANY n >= 4 (one block, Jacobi on the 2n x 9 design matrix). */
+size_t sfm_homography_npt_workspace_bytes(int32_t n);
+int sfm_homography_npt(const double *d_x1, const double *d_x2, int32_t n, double *d_H, void *d_ws,
+                       size_t ws_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -154,6 +154,33 @@ def gen_twoview():
     save("twoview.npz", **out)
 
 
+def gen_homography():
+    """Homography RANSAC: find_homography on 4 and on many points, and
+    get_homography_inliers on seeded synthetic pairs with the recorded random.sample stream."""
+    out = {}
+    rng = np.random.default_rng(41)
+    for tag, n, out_frac, thr, n_max in (("a", 500, 0.3, 30.0, 400), ("b", 120, 0.5, 5.0, 300)):
+        # planar scene: x2 = H_true x1 + noise, a fraction replaced by gross outliers
+        Ht = np.array([[0.9, 0.05, 30.0], [-0.04, 1.1, -12.0], [1e-5, -2e-5, 1.0]])
+        x1 = rng.uniform(0, 1000, (n, 2))
+        t = (Ht @ np.hstack([x1, np.ones((n, 1))]).T).T
+        x2 = t[:, :2] / t[:, 2:3] + rng.normal(0, 0.7, (n, 2))
+        bad = rng.random(n) < out_frac
+        x2[bad] = rng.uniform(0, 1000, (int(bad.sum()), 2))
+        idx = np.arange(1000, 1000 + n)
+        seed = 500 + n
+        samples = replay_samples(seed, n, 4, n_max)
+        random.seed(seed)
+        with np.errstate(all="ignore"):
+            H, inl = refH.get_homography_inliers(x1, x2, idx, threshold=thr, n_max=n_max)
+        Hall = refH.find_homography(x1[~bad], x2[~bad])
+        H4 = refH.find_homography(x1[:4], x2[:4])
+        out.update({f"x1_{tag}": x1, f"x2_{tag}": x2, f"idx_{tag}": idx, f"thr_{tag}": thr, f"seed_{tag}": seed,
+                    f"samples_{tag}": samples, f"H_{tag}": H, f"inl_{tag}": inl, f"good_{tag}": ~bad,
+                    f"Hall_{tag}": Hall, f"H4_{tag}": H4})
+    save("homography.npz", **out)
+
+
 def gen_pnp():
     out = {}
     for tag, n, ofrac, seed in (("a", 300, 0.0, 31), ("b", 2000, 0.10, 32), ("c", 12, 0.0, 33)):
@@ -234,6 +261,6 @@ def gen_ba():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["f8pt", "fransac", "p3data", "tri", "pnp", "ba", "twoview"]
+    which = sys.argv[1:] or ["f8pt", "fransac", "p3data", "tri", "pnp", "ba", "twoview", "homography"]
     for w in which:
         globals()["gen_" + w]()

@@ -350,3 +350,58 @@ def disambiguate_camera_pose(Cset, Rset, Xset):
     if best is None:
         return np.asarray(Cset[0]), np.asarray(Rset[0]), np.asarray(Xset[0]), 0, -1
     return np.array(Cset[best]), np.array(Rset[best]), np.array(Xset[best]), best, int(best_count)
+
+
+# ------------------------------------------------------------------ homography RANSAC (N2)
+def find_homography(image1_coords, image2_coords):
+    """GetHomographyInliers.py:4-82."""
+    p1, p2 = np.array(image1_coords, float), np.array(image2_coords, float)
+    n = len(p1)
+    if n < 4:
+        raise ValueError("At least 4 point correspondences are required for homography estimation")
+    m1, m2 = np.mean(p1, axis=0), np.mean(p2, axis=0)
+    c1, c2 = p1 - m1, p2 - m2
+    s1 = np.sqrt(2) / (np.mean(np.sqrt(np.sum(c1 ** 2, axis=1))) + 1e-8)
+    s2 = np.sqrt(2) / (np.mean(np.sqrt(np.sum(c2 ** 2, axis=1))) + 1e-8)
+    T1 = np.array([[s1, 0, -s1 * m1[0]], [0, s1, -s1 * m1[1]], [0, 0, 1]])
+    T2 = np.array([[s2, 0, -s2 * m2[0]], [0, s2, -s2 * m2[1]], [0, 0, 1]])
+    ones = np.ones((n, 1))
+    n1 = (T1 @ np.hstack([p1, ones]).T).T
+    n2 = (T2 @ np.hstack([p2, ones]).T).T
+    A = np.zeros((2 * n, 9))
+    x1, y1, x2, y2 = n1[:, 0], n1[:, 1], n2[:, 0], n2[:, 1]
+    A[0::2, 3], A[0::2, 4], A[0::2, 5] = -x1, -y1, -1
+    A[0::2, 6], A[0::2, 7], A[0::2, 8] = y2 * x1, y2 * y1, y2
+    A[1::2, 0], A[1::2, 1], A[1::2, 2] = x1, y1, 1
+    A[1::2, 6], A[1::2, 7], A[1::2, 8] = -x2 * x1, -x2 * y1, -x2
+    _, _, Vt = np.linalg.svd(A)
+    H = np.linalg.inv(T2) @ Vt[-1, :].reshape(3, 3) @ T1
+    return H / H[2, 2]
+
+
+def h_errors(H, points1, points2):
+    """GetHomographyInliers.py:139-146."""
+    n = len(points1)
+    t = (H @ np.hstack([points1, np.ones((n, 1))]).T).T
+    t2 = t[:, :2] / (t[:, 2:3] + 1e-8)
+    return np.sqrt(np.sum((t2 - points2) ** 2, axis=1))
+
+
+def h_ransac_detailed(points1, points2, threshold, samples):
+    """The loop of GetHomographyInliers.py:124-161 on given 4-index sample sets."""
+    p1, p2 = np.array(points1, float), np.array(points2, float)
+    h = len(samples)
+    Hs, counts = np.full((h, 9), np.nan), np.zeros(h, dtype=np.int64)
+    best_count, best_idx, mask_best, err_best = 0, -1, np.zeros(len(p1), bool), None
+    for k, s in enumerate(samples):
+        try:
+            with np.errstate(all="ignore"):
+                H = find_homography(p1[list(s)], p2[list(s)])
+                err = h_errors(H, p1, p2)
+            mask = err < threshold
+        except Exception:
+            continue
+        Hs[k], counts[k] = H.ravel(), int(mask.sum())
+        if counts[k] > best_count:
+            best_count, best_idx, mask_best, err_best = int(counts[k]), k, mask, err
+    return dict(H=Hs, counts=counts, best_idx=best_idx, best_count=best_count, mask=mask_best, err=err_best)

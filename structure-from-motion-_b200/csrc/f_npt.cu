@@ -36,42 +36,12 @@ __device__ __forceinline__ void block_sum(double (&v)[K], double *sred /* [32*K]
     }
 }
 
-__global__ void __launch_bounds__(NPT_THREADS)
-fundamental_npt_kernel(const double *__restrict__ x1, const double *__restrict__ x2, int n,
-                       double *__restrict__ A /* [9][n] */, double *__restrict__ Fout) {
-    __shared__ double sred[32 * 4];
-    __shared__ double V[9][9];
+// One-sided (Hestenes) Jacobi on the nine columns of A [9][n] (column-major, global workspace),
+// accumulating the rotations in V (shared, identity on entry). Returns the index of the column of
+// least norm -- V[:, jmin] is the right singular vector of the smallest singular value (Vt[-1]).
+// Every thread of the block gets the same value.
+__device__ int block_jacobi_null9(double *__restrict__ A, int n, double (*V)[9], double *sred) {
     const int tid = threadIdx.x;
-
-    double m[4] = {0, 0, 0, 0};
-    for (int i = tid; i < n; i += NPT_THREADS) {
-        m[0] += x1[2 * i]; m[1] += x1[2 * i + 1]; m[2] += x2[2 * i]; m[3] += x2[2 * i + 1];
-    }
-    block_sum<4>(m, sred);
-    const double inv_n = 1.0 / (double)n;
-    const double mx1 = m[0] * inv_n, my1 = m[1] * inv_n, mx2 = m[2] * inv_n, my2 = m[3] * inv_n;
-    double d[2] = {0, 0};
-    for (int i = tid; i < n; i += NPT_THREADS) {
-        double ax = x1[2 * i] - mx1, ay = x1[2 * i + 1] - my1;
-        double bx = x2[2 * i] - mx2, by = x2[2 * i + 1] - my2;
-        d[0] += sqrt(ax * ax + ay * ay);
-        d[1] += sqrt(bx * bx + by * by);
-    }
-    block_sum<2>(d, sred);
-    const double SQRT2 = 1.4142135623730951;
-    const double s1 = SQRT2 / (d[0] * inv_n + 1e-8), s2 = SQRT2 / (d[1] * inv_n + 1e-8);
-    const double tx1 = -s1 * mx1, ty1 = -s1 * my1, tx2 = -s2 * mx2, ty2 = -s2 * my2;
-
-    for (int i = tid; i < n; i += NPT_THREADS) {
-        double u1 = s1 * x1[2 * i] + tx1, v1 = s1 * x1[2 * i + 1] + ty1;
-        double u2 = s2 * x2[2 * i] + tx2, v2 = s2 * x2[2 * i + 1] + ty2;
-        A[0 * (size_t)n + i] = u1 * u2; A[1 * (size_t)n + i] = u1 * v2; A[2 * (size_t)n + i] = u1;
-        A[3 * (size_t)n + i] = v1 * u2; A[4 * (size_t)n + i] = v1 * v2; A[5 * (size_t)n + i] = v1;
-        A[6 * (size_t)n + i] = u2;      A[7 * (size_t)n + i] = v2;      A[8 * (size_t)n + i] = 1.0;
-    }
-    if (tid < 81) V[tid / 9][tid % 9] = (tid / 9 == tid % 9) ? 1.0 : 0.0;
-    __syncthreads();
-
     for (int sweep = 0; sweep < 60; ++sweep) {
         int rotated = 0;
         for (int p = 0; p < 8; ++p) {
@@ -124,9 +94,49 @@ fundamental_npt_kernel(const double *__restrict__ x1, const double *__restrict__
             nrm[3 * r] = t3[0]; nrm[3 * r + 1] = t3[1]; nrm[3 * r + 2] = t3[2];
         }
     }
+    int jmin = 0;
+    for (int c = 1; c < 9; ++c) if (nrm[c] < nrm[jmin]) jmin = c;
+    return jmin;
+}
+
+__global__ void __launch_bounds__(NPT_THREADS)
+fundamental_npt_kernel(const double *__restrict__ x1, const double *__restrict__ x2, int n,
+                       double *__restrict__ A /* [9][n] */, double *__restrict__ Fout) {
+    __shared__ double sred[32 * 4];
+    __shared__ double V[9][9];
+    const int tid = threadIdx.x;
+
+    double m[4] = {0, 0, 0, 0};
+    for (int i = tid; i < n; i += NPT_THREADS) {
+        m[0] += x1[2 * i]; m[1] += x1[2 * i + 1]; m[2] += x2[2 * i]; m[3] += x2[2 * i + 1];
+    }
+    block_sum<4>(m, sred);
+    const double inv_n = 1.0 / (double)n;
+    const double mx1 = m[0] * inv_n, my1 = m[1] * inv_n, mx2 = m[2] * inv_n, my2 = m[3] * inv_n;
+    double d[2] = {0, 0};
+    for (int i = tid; i < n; i += NPT_THREADS) {
+        double ax = x1[2 * i] - mx1, ay = x1[2 * i + 1] - my1;
+        double bx = x2[2 * i] - mx2, by = x2[2 * i + 1] - my2;
+        d[0] += sqrt(ax * ax + ay * ay);
+        d[1] += sqrt(bx * bx + by * by);
+    }
+    block_sum<2>(d, sred);
+    const double SQRT2 = 1.4142135623730951;
+    const double s1 = SQRT2 / (d[0] * inv_n + 1e-8), s2 = SQRT2 / (d[1] * inv_n + 1e-8);
+    const double tx1 = -s1 * mx1, ty1 = -s1 * my1, tx2 = -s2 * mx2, ty2 = -s2 * my2;
+
+    for (int i = tid; i < n; i += NPT_THREADS) {
+        double u1 = s1 * x1[2 * i] + tx1, v1 = s1 * x1[2 * i + 1] + ty1;
+        double u2 = s2 * x2[2 * i] + tx2, v2 = s2 * x2[2 * i + 1] + ty2;
+        A[0 * (size_t)n + i] = u1 * u2; A[1 * (size_t)n + i] = u1 * v2; A[2 * (size_t)n + i] = u1;
+        A[3 * (size_t)n + i] = v1 * u2; A[4 * (size_t)n + i] = v1 * v2; A[5 * (size_t)n + i] = v1;
+        A[6 * (size_t)n + i] = u2;      A[7 * (size_t)n + i] = v2;      A[8 * (size_t)n + i] = 1.0;
+    }
+    if (tid < 81) V[tid / 9][tid % 9] = (tid / 9 == tid % 9) ? 1.0 : 0.0;
+    __syncthreads();
+
+    const int jmin = block_jacobi_null9(A, n, V, sred);
     if (tid == 0) {
-        int jmin = 0;
-        for (int c = 1; c < 9; ++c) if (nrm[c] < nrm[jmin]) jmin = c;
         double f[9];
         for (int r = 0; r < 9; ++r) f[r] = V[r][jmin];
         rank2_project3(f);
@@ -146,6 +156,66 @@ fundamental_npt_kernel(const double *__restrict__ x1, const double *__restrict__
     }
 }
 
+// find_homography (GetHomographyInliers.py:4-82) for n >= 4 correspondences: same block-wide scheme,
+// design matrix [9][2n].
+__global__ void __launch_bounds__(NPT_THREADS)
+homography_npt_kernel(const double *__restrict__ x1, const double *__restrict__ x2, int n,
+                      double *__restrict__ A /* [9][2n] */, double *__restrict__ Hout) {
+    __shared__ double sred[32 * 4];
+    __shared__ double V[9][9];
+    const int tid = threadIdx.x;
+    double m[4] = {0, 0, 0, 0};
+    for (int i = tid; i < n; i += NPT_THREADS) {
+        m[0] += x1[2 * i]; m[1] += x1[2 * i + 1]; m[2] += x2[2 * i]; m[3] += x2[2 * i + 1];
+    }
+    block_sum<4>(m, sred);
+    const double inv_n = 1.0 / (double)n;
+    const double mx1 = m[0] * inv_n, my1 = m[1] * inv_n, mx2 = m[2] * inv_n, my2 = m[3] * inv_n;
+    double d[2] = {0, 0};
+    for (int i = tid; i < n; i += NPT_THREADS) {
+        double ax = x1[2 * i] - mx1, ay = x1[2 * i + 1] - my1;
+        double bx = x2[2 * i] - mx2, by = x2[2 * i + 1] - my2;
+        d[0] += sqrt(ax * ax + ay * ay);
+        d[1] += sqrt(bx * bx + by * by);
+    }
+    block_sum<2>(d, sred);
+    const double SQRT2 = 1.4142135623730951;
+    const double s1 = SQRT2 / (d[0] * inv_n + 1e-8), s2 = SQRT2 / (d[1] * inv_n + 1e-8);
+    const double tx1 = -s1 * mx1, ty1 = -s1 * my1, tx2 = -s2 * mx2, ty2 = -s2 * my2;
+    const size_t m2 = 2 * (size_t)n;
+    for (int i = tid; i < n; i += NPT_THREADS) {
+        const double u1 = s1 * x1[2 * i] + tx1, v1 = s1 * x1[2 * i + 1] + ty1;
+        const double u2 = s2 * x2[2 * i] + tx2, v2 = s2 * x2[2 * i + 1] + ty2;
+        const size_t r0 = 2 * (size_t)i, r1 = r0 + 1;
+        A[0 * m2 + r0] = 0.0; A[1 * m2 + r0] = 0.0; A[2 * m2 + r0] = 0.0;
+        A[3 * m2 + r0] = -u1; A[4 * m2 + r0] = -v1; A[5 * m2 + r0] = -1.0;
+        A[6 * m2 + r0] = v2 * u1; A[7 * m2 + r0] = v2 * v1; A[8 * m2 + r0] = v2;
+        A[0 * m2 + r1] = u1; A[1 * m2 + r1] = v1; A[2 * m2 + r1] = 1.0;
+        A[3 * m2 + r1] = 0.0; A[4 * m2 + r1] = 0.0; A[5 * m2 + r1] = 0.0;
+        A[6 * m2 + r1] = -u2 * u1; A[7 * m2 + r1] = -u2 * v1; A[8 * m2 + r1] = -u2;
+    }
+    if (tid < 81) V[tid / 9][tid % 9] = (tid / 9 == tid % 9) ? 1.0 : 0.0;
+    __syncthreads();
+    const int jmin = block_jacobi_null9(A, (int)m2, V, sred);
+    if (tid == 0) {
+        double f[9], g[9], o[9];
+        for (int r = 0; r < 9; ++r) f[r] = V[r][jmin];
+        for (int r = 0; r < 3; ++r) {
+            g[3 * r + 0] = f[3 * r + 0] * s1;
+            g[3 * r + 1] = f[3 * r + 1] * s1;
+            g[3 * r + 2] = f[3 * r + 0] * tx1 + f[3 * r + 1] * ty1 + f[3 * r + 2];
+        }
+        const double is2 = 1.0 / s2;
+        for (int c = 0; c < 3; ++c) {
+            o[0 + c] = is2 * g[0 + c] + mx2 * g[6 + c];
+            o[3 + c] = is2 * g[3 + c] + my2 * g[6 + c];
+            o[6 + c] = g[6 + c];
+        }
+        const double inv = o[8];
+        for (int i = 0; i < 9; ++i) Hout[i] = o[i] / inv;
+    }
+}
+
 }  // namespace sfm
 
 using namespace sfm;
@@ -160,6 +230,19 @@ extern "C" int sfm_fundamental_npt(const double *d_x1, const double *d_x2, int32
     if (ws_bytes < sfm_fundamental_npt_workspace_bytes(n)) return SFM_E_WORKSPACE;
     fundamental_npt_kernel<<<1, NPT_THREADS, 0, as_stream(stream)>>>(
         d_x1, d_x2, n, reinterpret_cast<double *>(d_ws), d_F);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+extern "C" size_t sfm_homography_npt_workspace_bytes(int32_t n) {
+    return n > 0 ? sizeof(double) * 18 * (size_t)n : 0;
+}
+
+extern "C" int sfm_homography_npt(const double *d_x1, const double *d_x2, int32_t n, double *d_H, void *d_ws,
+                                  size_t ws_bytes, void *stream) {
+    if (!d_x1 || !d_x2 || !d_H || !d_ws || n < 4) return SFM_E_INVALID;
+    if (ws_bytes < sfm_homography_npt_workspace_bytes(n)) return SFM_E_WORKSPACE;
+    homography_npt_kernel<<<1, NPT_THREADS, 0, as_stream(stream)>>>(d_x1, d_x2, n, reinterpret_cast<double *>(d_ws), d_H);
     SFM_LAUNCH_CHECK();
     return SFM_OK;
 }
