@@ -283,6 +283,19 @@ size_t sfm_homography_npt_workspace_bytes(int32_t n);
 int sfm_homography_npt(const double *d_x1, const double *d_x2, int32_t n, double *d_H, void *d_ws,
                        size_t ws_bytes, void *stream);
 
+/* ---- N3: bundle-adjustment problem assembly on the device ---------------------------
+ * Replaces BundleAdjustment.py:148-176. Inputs are the wrapper's dense arrays on the device:
+ *   d_valid [F] uint8 (filtered_world_coords == 1), d_flags [F,row_stride] uint8 (== 1 means observed),
+ *   d_fx, d_fy [F,row_stride] f64, d_world [F,3] f64; cameras 0..n_cams-1 are used (:156).
+ * Outputs in the reference's order (valid rows ascending, cameras ascending): d_cam_idx, d_pt_idx, d_obs
+ * (capacity F*n_cams entries), d_pts [F,3] and d_valid_rows [F] (compacted, capacity F),
+ * d_totals2 = (number of points, number of observations). */
+size_t sfm_ba_assemble_workspace_bytes(int32_t n_features);
+int sfm_ba_assemble(const uint8_t *d_valid, const uint8_t *d_flags, const double *d_fx, const double *d_fy,
+                    const double *d_world, int32_t n_features, int32_t row_stride, int32_t n_cams,
+                    int32_t *d_cam_idx, int32_t *d_pt_idx, double *d_obs, double *d_pts,
+                    int32_t *d_valid_rows, int32_t *d_totals2, void *d_ws, size_t ws_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

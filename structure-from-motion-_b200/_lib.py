@@ -44,6 +44,9 @@ SIGNATURES = {
                                c_f64p, c_vp, c_f64p, c_vp]),
     "sfm_homography_npt_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "sfm_homography_npt": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_vp, C.c_size_t, c_vp]),
+    "sfm_ba_assemble_workspace_bytes": (C.c_size_t, [C.c_int32]),
+    "sfm_ba_assemble": (C.c_int, [c_vp, c_vp, c_f64p, c_f64p, c_f64p, C.c_int32, C.c_int32, C.c_int32, c_i32p, c_i32p,
+                                  c_f64p, c_f64p, c_i32p, c_i32p, c_vp, C.c_size_t, c_vp]),
     "sfm_two_view_configs": (C.c_int, [c_f64p, c_vp, c_f64p, c_f64p, c_i32p, c_vp]),
     "sfm_cheirality_count": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_i32p, c_vp]),
     "sfm_two_view_pose": (C.c_int, [c_f64p, c_vp, c_f64p, c_f64p, C.c_int32, c_f64p, c_f64p, c_f64p,

@@ -170,6 +170,41 @@ def build_problem(all_world_coords, filtered_world_coords, feature_x, feature_y,
                 pt_idx=pt_local.astype(np.int32), obs=obs, cams=cams, pts=pts)
 
 
+def build_problem_device(all_world_coords, filtered_world_coords, feature_x, feature_y, filtered_feature_flags,
+                         n_cameras):
+    """BundleAdjustment.py:148-176 on the device: the dense (n_features x n_images) arrays
+    go up once, the point-sorted observation list is built there (sfm_ba_assemble) and stays there.
+    Returns None when there is nothing to optimise, else dict of device tensors cam_idx, pt_idx, obs, pts,
+    valid_rows (trimmed views) and the host counts n_points, n_obs."""
+    lib = _lib.load()
+    valid = np.ascontiguousarray(np.asarray(filtered_world_coords).reshape(-1) == 1, np.uint8)
+    flags = np.asarray(filtered_feature_flags)
+    F, stride = int(flags.shape[0]), int(flags.shape[1])
+    if F == 0 or len(valid) != F:
+        return None
+    n_cameras = int(min(n_cameras, stride))
+    d_valid = device.to_device(valid, np.uint8)
+    d_flags = device.to_device(np.ascontiguousarray(flags == 1, np.uint8), np.uint8)
+    d_fx, d_fy = device.to_device(np.asarray(feature_x, np.float64)), device.to_device(np.asarray(feature_y, np.float64))
+    d_world = device.to_device(np.asarray(all_world_coords, np.float64).reshape(F, 3))
+    cap = max(1, F * max(n_cameras, 1))
+    d_cam, d_pt = device.empty((cap,), torch.int32), device.empty((cap,), torch.int32)
+    d_obs, d_pts = device.empty((cap, 2), torch.float64), device.empty((F, 3), torch.float64)
+    d_rows, d_tot = device.empty((F,), torch.int32), device.empty((2,), torch.int32)
+    nbytes = int(lib.sfm_ba_assemble_workspace_bytes(F))
+    ws = device.empty((nbytes,), torch.uint8)
+    rc = lib.sfm_ba_assemble(device.ptr(d_valid), device.ptr(d_flags), device.ptr(d_fx), device.ptr(d_fy),
+                             device.ptr(d_world), F, stride, n_cameras, device.ptr(d_cam), device.ptr(d_pt),
+                             device.ptr(d_obs), device.ptr(d_pts), device.ptr(d_rows), device.ptr(d_tot), device.ptr(ws),
+                             nbytes, device.stream())
+    _lib.check(rc, "sfm_ba_assemble")
+    n_points, n_obs = (int(v) for v in d_tot.cpu().numpy())
+    if n_points == 0 or n_obs == 0:
+        return None
+    return dict(n_cameras=n_cameras, n_points=n_points, n_obs=n_obs, cam_idx=d_cam[:n_obs], pt_idx=d_pt[:n_obs],
+                obs=d_obs[:n_obs], pts=d_pts[:n_points], valid_rows=d_rows[:n_points])
+
+
 def perform_bundle_adjustment(all_world_coords, filtered_world_coords, feature_x, feature_y,
                               filtered_feature_flags, R_set, C_set, K, cam_index, tol=REF_TOL, info=None):
     """Drop-in for BundleAdjustment.py:113-242 -> (R_set_opt, C_set_opt, all_world_coords_opt)."""
