@@ -755,6 +755,160 @@ ba_schur_rows_kernel(const double *__restrict__ W, int nobs, const int32_t *__re
     if (lane >= 18 && lane < 24) atomicAdd(&gred[6 * ci + lane - 18], gacc);
 }
 
+// K10s: the Schur complement accumulated in SHARED memory, for problems whose camera count lets the
+// lower block triangle of S be cut into a few row ranges of <= ~190 KB (up to ~100 cameras: the
+// reference's regime, 6 cameras on its own data, 50 at BASELINE config 3). CTA (range t, slice g)
+// streams slice g of the point-sorted observation list through a small staging buffer -- W planes
+// with coalesced loads, Y = W V^-1 computed once per observation -- and adds -Y_i W_j^T for the
+// block rows of its range into its shared-memory copy; warp w of 16 owns the rows with
+// (ci - first row) % 16 == w, so no two warps ever touch the same block and nothing is atomic until
+// the final flush (36 atomics per touched block and CTA instead of 36 per point and camera pair:
+// 23x fewer at config 3). Lane = (observation j of the track, block column q), five j per pass.
+constexpr int SS_THREADS = 512;
+constexpr int SS_WARPS = SS_THREADS / 32;
+constexpr int SS_LDW = 97;                      // row stride of the staged W planes (odd: spreads the banks)
+constexpr int SS_OB = 96;                       // observations per staged batch (whole points only)
+constexpr int SS_MAX_RANGES = 8;
+constexpr size_t SS_STAGE_BYTES = sizeof(double) * (18 * SS_LDW + SS_OB * 18) + sizeof(int) * (4 * SS_OB + 8);
+
+struct SchurRanges {
+    int n;                                      // number of row ranges
+    int row[SS_MAX_RANGES + 1];                 // range t = block rows row[t] .. row[t+1]-1
+};
+
+// plan-time statistics: longest track and whether any track names one camera twice
+__global__ void ba_track_stats_kernel(const int32_t *__restrict__ pt_ptr, const int32_t *__restrict__ cam_idx,
+                                      int npts, int *__restrict__ stats) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npts) return;
+    const int o0 = pt_ptr[p], k = pt_ptr[p + 1] - o0;
+    atomicMax(&stats[0], k);
+    if (k > 64) { atomicOr(&stats[1], 1); return; }          // not examined: assume duplicates
+    for (int a = 1; a < k; ++a)
+        for (int b = 0; b < a; ++b)
+            if (cam_idx[o0 + a] == cam_idx[o0 + b]) { atomicOr(&stats[1], 1); return; }
+}
+
+template <bool DUPS>
+__global__ void __launch_bounds__(SS_THREADS, 1)
+ba_schur_smem_kernel(const double *__restrict__ W, int nobs, const int32_t *__restrict__ cam_idx,
+                     const int32_t *__restrict__ pt_idx, const int32_t *__restrict__ pt_ptr, int npts,
+                     const double *__restrict__ Vinv, const double *__restrict__ bp, SchurRanges rg, int nslices,
+                     double *__restrict__ S, size_t ld, double *__restrict__ gred, int skip) {
+    extern __shared__ __align__(16) double ss_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int t = blockIdx.x % rg.n, g = blockIdx.x / rg.n;
+    const int r0 = rg.row[t], r1 = rg.row[t + 1];
+    const int tri0 = r0 * (r0 + 1) / 2, nblk = r1 * (r1 + 1) / 2 - tri0;
+    double *acc = ss_smem, *stW = acc + (size_t)nblk * 36, *stY = stW + 18 * SS_LDW;   // 18 * 97 doubles: stY stays 16-byte aligned
+    int *stC = reinterpret_cast<int *>(stY + SS_OB * 18), *stS = stC + SS_OB, *stE = stS + SS_OB, *stPt = stE + SS_OB;
+    int *ctl = stPt + SS_OB;
+    for (int e = tid; e < nblk * 36; e += SS_THREADS) acc[e] = 0.0;
+    const int per = (npts + nslices - 1) / nslices;
+    const int p0 = g * per, p1 = min(npts, p0 + per);
+    const int grp = lane / 6, q = lane - 6 * grp;            // grp == 5: lanes 30, 31 idle
+    for (int pb = p0; pb < p1;) {
+        __syncthreads();                                      // the previous batch is consumed (and acc is zero)
+        if (warp == 0) {
+            const int o0 = pt_ptr[pb];
+            const int pe = min(pb + lane + 1, p1);
+            const bool ok = (pb + lane < p1) && (pt_ptr[pe] - o0 <= SS_OB);
+            const int nb = __popc(__ballot_sync(0xffffffffu, ok));   // whole points that fit (>= 1: the
+            if (lane == 0) {                                          // host checked the longest track)
+                ctl[0] = max(nb, 1);
+                ctl[1] = pt_ptr[pb + max(nb, 1)] - o0;
+                ctl[2] = o0;
+            }
+        }
+        __syncthreads();
+        const int np_b = ctl[0], nob = min(ctl[1], SS_OB), o0 = ctl[2];
+        for (int i = tid; i < nob; i += SS_THREADS) {
+            const int p = pt_idx[o0 + i];
+            stC[i] = cam_idx[o0 + i];
+            stPt[i] = p;
+            stS[i] = pt_ptr[p] - o0;
+            stE[i] = pt_ptr[p + 1] - o0;
+        }
+        for (int e = tid; e < nob * 18; e += SS_THREADS) {
+            const int rc = e / nob, i = e - rc * nob;
+            stW[rc * SS_LDW + i] = W[(size_t)rc * nobs + o0 + i];
+        }
+        __syncthreads();
+        if (!(skip & 2))
+        for (int e = tid; e < nob * 6; e += SS_THREADS) {     // Y_i = W_i V^-1 (row r), g_red -= W_i b_p
+            const int i = e / 6, r = e - 6 * i, p = stPt[i];
+            const double w0 = stW[(3 * r) * SS_LDW + i], w1 = stW[(3 * r + 1) * SS_LDW + i], w2 = stW[(3 * r + 2) * SS_LDW + i];
+            const double *vi = Vinv + 6 * (size_t)p;
+            stY[i * 18 + 3 * r + 0] = w0 * vi[0] + w1 * vi[1] + w2 * vi[3];
+            stY[i * 18 + 3 * r + 1] = w0 * vi[1] + w1 * vi[2] + w2 * vi[4];
+            stY[i * 18 + 3 * r + 2] = w0 * vi[3] + w1 * vi[4] + w2 * vi[5];
+            if (t == 0) {
+                const double *b = bp + 3 * (size_t)p;
+                atomicAdd(&gred[6 * stC[i] + r], -(w0 * b[0] + w1 * b[1] + w2 * b[2]));
+            }
+        }
+        __syncthreads();
+        if (!(skip & 1))
+        for (int ib = 0; ib < nob; ib += 32) {
+            const int i = ib + lane;
+            const int c = i < nob ? stC[i] : -1;
+            const bool owned = c >= r0 && c < r1 && ((c - r0) & (SS_WARPS - 1)) == warp;
+            unsigned om = __ballot_sync(0xffffffffu, owned);
+            while (om) {
+                const int src = __ffs(om) - 1;
+                om &= om - 1;
+                const int ii = ib + src;
+                const int ci = __shfl_sync(0xffffffffu, c, src);
+                const int s_ = stS[ii], e_ = stE[ii];
+                double Y[18];
+                {
+                    const double2 *y2 = reinterpret_cast<const double2 *>(stY + ii * 18);
+#pragma unroll
+                    for (int k = 0; k < 9; ++k) { const double2 v = y2[k]; Y[2 * k] = v.x; Y[2 * k + 1] = v.y; }
+                }
+                double *rowbase = acc + (size_t)(ci * (ci + 1) / 2 - tri0) * 36 + q;
+                for (int t0 = s_; t0 < e_; t0 += 5) {
+                    const int j = t0 + grp;
+                    const bool have = grp < 5 && j < e_;
+                    const int cj = have ? stC[j] : 0x7fffffff;
+                    const bool ok = have && cj <= ci;
+                    double w0 = 0.0, w1 = 0.0, w2 = 0.0;
+                    if (!__any_sync(0xffffffffu, ok)) continue;
+                    if (ok) { w0 = stW[(3 * q) * SS_LDW + j]; w1 = stW[(3 * q + 1) * SS_LDW + j]; w2 = stW[(3 * q + 2) * SS_LDW + j]; }
+                    if (!DUPS) {
+                        if (ok) {
+                            double *a = rowbase + (size_t)cj * 36;
+#pragma unroll
+                            for (int r = 0; r < 6; ++r) a[6 * r] -= Y[3 * r] * w0 + Y[3 * r + 1] * w1 + Y[3 * r + 2] * w2;
+                        }
+                    } else {                                  // a camera twice in one track: one group at a time
+                        for (int gg = 0; gg < 5; ++gg) {
+                            if (ok && grp == gg) {
+                                double *a = rowbase + (size_t)cj * 36;
+#pragma unroll
+                                for (int r = 0; r < 6; ++r) a[6 * r] -= Y[3 * r] * w0 + Y[3 * r + 1] * w1 + Y[3 * r + 2] * w2;
+                            }
+                            __syncwarp();
+                        }
+                    }
+                }
+            }
+        }
+        pb += np_b;
+    }
+    __syncthreads();
+    for (int ci = r0; ci < r1; ++ci) {
+        const double *base = acc + (size_t)(ci * (ci + 1) / 2 - tri0) * 36;
+        for (int e = tid; e < (ci + 1) * 36; e += SS_THREADS) {
+            const double v = base[e];
+            if (v != 0.0) {
+                const int cj = e / 36, el = e - 36 * cj, r = el / 6, qq = el - 6 * r;
+                atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * cj + qq], v);
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------ update (K12)
 // partial sums layout (4 doubles): [s.g, |D s|^2, |D x_new|^2, |D x_cur|^2]
 __global__ void __launch_bounds__(256)
@@ -895,6 +1049,49 @@ static int schur_window(int nc) {
     return nc <= 48 ? nc : 40;       // 40 blocks per warp: two 8-warp CTAs per SM
 }
 
+// K10s applies when the lower block triangle of S splits into at most SS_MAX_RANGES row ranges that
+// fit shared memory next to the staging buffer, and no track is longer than a staged batch.
+static bool schur_smem_ranges(int nc, int max_track, SchurRanges &rg) {
+    // Measured on B200 at config 3 (tools/ba_probe.py): K10a + K10s 0.22 ms per trial against 0.17 ms for
+    // the point-major K10 -- the pair phase is latency bound (each warp walks its block rows serially,
+    // ~3000 cycles per owned observation), so the L2 atomic path stays the default and this kernel is
+    // opt-in (SFM_SCHUR_SMEM=1) until its pair phase is pipelined.
+    static int off = -1;
+    if (off < 0) {
+        const char *e = getenv("SFM_SCHUR_SMEM");
+        off = (e && e[0] == '1') ? 0 : 1;
+    }
+    if (off || max_track > SS_OB || max_track < 1) return false;
+    const long long cap_blocks = (long long)((BA_SMEM_MAX - SS_STAGE_BYTES) / (36 * sizeof(double)));
+    rg.n = 0;
+    rg.row[0] = 0;
+    int c = 0;
+    while (c < nc) {
+        if (rg.n == SS_MAX_RANGES) return false;
+        long long blocks = 0;
+        int e = c;
+        while (e < nc && blocks + (e + 1) <= cap_blocks) { blocks += e + 1; ++e; }
+        if (e == c) return false;                               // one block row alone does not fit
+        rg.row[++rg.n] = e;
+        c = e;
+    }
+    // balance: equal block counts per range instead of greedy-full ranges
+    if (rg.n > 1) {
+        const long long total = (long long)nc * (nc + 1) / 2;
+        int cc = 0;
+        for (int t = 1; t < rg.n; ++t) {
+            const long long target = total * t / rg.n;
+            while ((long long)cc * (cc + 1) / 2 < target) ++cc;
+            rg.row[t] = cc;
+        }
+        for (int t = 0; t < rg.n; ++t) {
+            const long long b = (long long)rg.row[t + 1] * (rg.row[t + 1] + 1) / 2 - (long long)rg.row[t] * (rg.row[t] + 1) / 2;
+            if (b > cap_blocks || rg.row[t + 1] <= rg.row[t]) return false;
+        }
+    }
+    return true;
+}
+
 // observations per warp of K10b: enough warps to fill the GPU several times over, few enough that the
 // window flushes (36 atomics per touched block and warp) stay small next to the accumulation
 static int schur_slice(int nobs) {
@@ -911,7 +1108,7 @@ static int schur_slice(int nobs) {
 }
 
 struct BAPlan {
-    int nc, np, nobs, npad, nchunks, grid_obs, grid_pts, obs_threads;
+    int nc, np, nobs, npad, nchunks, grid_obs, grid_pts, obs_threads, max_track, has_dup;
     bool smem_cams;
     size_t ld, cam_smem;
     // index structures
@@ -1082,13 +1279,18 @@ static int ba_build_index(BAPlan &pl, const double2 *obs, const int32_t *cam_idx
     SFM_LAUNCH_CHECK();
     ba_gather_cam_major_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(pl.perm, obs, pt_idx, nobs, pl.obs_c, pl.pt_c);
     SFM_LAUNCH_CHECK();
+    ba_track_stats_kernel<<<ceil_div(np, 256), 256, 0, st>>>(pl.pt_ptr, cam_idx, np, pl.flags + 8);
+    SFM_LAUNCH_CHECK();
     // chunk table on the host
     std::vector<int32_t> cam_ptr(nc + 1);
-    int flag0 = 0;
+    int flag0 = 0, stats[2] = {0, 0};
+    SFM_CUDA_TRY(cudaMemcpyAsync(stats, pl.flags + 8, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
     SFM_CUDA_TRY(cudaMemcpyAsync(cam_ptr.data(), pl.cam_ptr, sizeof(int32_t) * (nc + 1), cudaMemcpyDeviceToHost, st));
     SFM_CUDA_TRY(cudaMemcpyAsync(&flag0, pl.flags, sizeof(int), cudaMemcpyDeviceToHost, st));
     SFM_CUDA_TRY(cudaStreamSynchronize(st));
     if (flag0) return SFM_E_INVALID;        // indices out of range or not sorted by point
+    pl.max_track = stats[0];
+    pl.has_dup = stats[1];
     std::vector<int32_t> ccam, cbeg, cend, cptr(nc + 1);
     for (int c = 0; c < nc; ++c) {
         cptr[c] = (int32_t)ccam.size();
@@ -1133,7 +1335,7 @@ static bool g_attrs_set = false;
 
 struct PlanKey {
     const void *ws, *cam_idx;
-    int nc, np, nobs, nchunks;
+    int nc, np, nobs, nchunks, max_track, has_dup;
 };
 static std::mutex g_plan_mu;
 static std::vector<PlanKey> g_plans;
@@ -1148,13 +1350,15 @@ static int ba_acquire_index(BAPlan &pl, bool reuse, const void *d_ws, const doub
         for (const PlanKey &pk : g_plans)
             if (pk.ws == d_ws && pk.nc == n_cams && pk.np == n_pts && pk.nobs == n_obs && pk.cam_idx == d_cam_idx) {
                 pl.nchunks = pk.nchunks;
+                pl.max_track = pk.max_track;
+                pl.has_dup = pk.has_dup;
                 return SFM_OK;
             }
     }
     int rc = ba_build_index(pl, obs, d_cam_idx, d_pt_idx, st);
     if (rc != SFM_OK) return rc;
     std::lock_guard<std::mutex> g(g_plan_mu);
-    PlanKey pk{d_ws, d_cam_idx, n_cams, n_pts, n_obs, pl.nchunks};
+    PlanKey pk{d_ws, d_cam_idx, n_cams, n_pts, n_obs, pl.nchunks, pl.max_track, pl.has_dup};
     bool found = false;
     for (PlanKey &q : g_plans)
         if (q.ws == d_ws) { q = pk; found = true; }
@@ -1287,7 +1491,34 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
                                                                                            pl.ld, lambda, pl.S);
             SFM_LAUNCH_CHECK();
         }
-        if (schur_by_rows()) {
+        SchurRanges rg;
+        if (!schur_by_rows() && schur_smem_ranges(nc, pl.max_track, rg)) {
+            ba_point_prep_kernel<<<ceil_div(np, 256), 256, 0, st>>>(pl.V, pl.gp, pl.Dp, np, lambda, update_D, first_lin,
+                                                                   pl.Vinv, pl.bp, pl.gmax, pl.flags + 1);
+            SFM_LAUNCH_CHECK();
+            const int nslices = std::max(1, sm_count() / rg.n);
+            size_t smem = 0;
+            for (int t = 0; t < rg.n; ++t) {
+                const size_t b = (size_t)rg.row[t + 1] * (rg.row[t + 1] + 1) / 2 - (size_t)rg.row[t] * (rg.row[t] + 1) / 2;
+                smem = std::max(smem, b * 36 * sizeof(double) + SS_STAGE_BYTES);
+            }
+            static int ss_skip = getenv("SFM_SS_SKIP") ? atoi(getenv("SFM_SS_SKIP")) : 0;   // timing experiments only
+            static bool attr = false;
+            if (!attr) {
+                cudaFuncSetAttribute(ba_schur_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BA_SMEM_MAX);
+                cudaFuncSetAttribute(ba_schur_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BA_SMEM_MAX);
+                attr = true;
+            }
+            if (pl.has_dup)
+                ba_schur_smem_kernel<true><<<rg.n * nslices, SS_THREADS, smem, st>>>(
+                    pl.W, nobs, d_cam_idx, d_pt_idx, pl.pt_ptr, np, pl.Vinv, pl.bp, rg, nslices, pl.S, pl.ld,
+                    pl.S + (size_t)pl.npad * pl.ld, ss_skip);
+            else
+                ba_schur_smem_kernel<false><<<rg.n * nslices, SS_THREADS, smem, st>>>(
+                    pl.W, nobs, d_cam_idx, d_pt_idx, pl.pt_ptr, np, pl.Vinv, pl.bp, rg, nslices, pl.S, pl.ld,
+                    pl.S + (size_t)pl.npad * pl.ld, ss_skip);
+            SFM_LAUNCH_CHECK();
+        } else if (schur_by_rows()) {
             ba_point_prep_kernel<<<ceil_div(np, 256), 256, 0, st>>>(pl.V, pl.gp, pl.Dp, np, lambda, update_D, first_lin,
                                                                    pl.Vinv, pl.bp, pl.gmax, pl.flags + 1);
             SFM_LAUNCH_CHECK();
