@@ -486,7 +486,9 @@ ba_schur_kernel(const double *__restrict__ W, int nobs, const int32_t *__restric
                     const int cj = c_[j];
                     const double *yr = y_ + i * 18 + 3 * r, *wq = w_ + j * 18 + 3 * q;
                     double val = -(yr[0] * wq[0] + yr[1] * wq[1] + yr[2] * wq[2]);
-                    if (ci > cj || j == i) {
+                    if (j == i) {                  // own diagonal block: K11 reads its lower triangle only
+                        if (q <= r) atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * ci + q], val);
+                    } else if (ci > cj) {
                         atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * cj + q], val);
                     } else if (ci < cj) {
                         atomicAdd(&S[(size_t)(6 * cj + q) * ld + 6 * ci + r], val);
@@ -519,7 +521,9 @@ ba_schur_kernel(const double *__restrict__ W, int nobs, const int32_t *__restric
                     double y2 = w0 * vi[3] + w1 * vi[4] + w2 * vi[5];
                     double val = -(y0 * W[(size_t)(3 * q) * nobs + oj] + y1 * W[(size_t)(3 * q + 1) * nobs + oj] +
                                    y2 * W[(size_t)(3 * q + 2) * nobs + oj]);
-                    if (ci > cj || j == i) {
+                    if (j == i) {
+                        if (q <= r) atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * ci + q], val);
+                    } else if (ci > cj) {
                         atomicAdd(&S[(size_t)(6 * ci + r) * ld + 6 * cj + q], val);
                     } else if (ci < cj) {
                         atomicAdd(&S[(size_t)(6 * cj + q) * ld + 6 * ci + r], val);
