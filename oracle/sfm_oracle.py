@@ -405,3 +405,16 @@ def h_ransac_detailed(points1, points2, threshold, samples):
         if counts[k] > best_count:
             best_count, best_idx, mask_best, err_best = int(counts[k]), k, mask, err
     return dict(H=Hs, counts=counts, best_idx=best_idx, best_count=best_count, mask=mask_best, err=err_best)
+
+
+def get_homography_inliers(image1_coords_org, image2_coords_org, idx, threshold=30, n_max=1000):
+    """GetHomographyInliers.py:85-165 drawing from the global `random` stream (:126)."""
+    p1, p2, idx = np.array(image1_coords_org), np.array(image2_coords_org), np.array(idx)
+    n = len(p1)
+    if n < 4:
+        return None, np.array([])
+    samples = draw_samples(n, 4, n_max)
+    r = h_ransac_detailed(p1, p2, threshold, samples)
+    if r["best_idx"] < 0 or r["best_count"] == 0:
+        return None, np.array([])
+    return r["H"][r["best_idx"]].reshape(3, 3), idx[np.where(r["mask"])[0]]
