@@ -268,6 +268,10 @@ def run_ours(args, rank, world):
                 out["ba"] = bench_ba.run_single_gpu(args, peaks, peak_src, flush)
                 out["ba"]["cpu_baseline"] = bench_ba.cpu_baseline()
                 out["gpu_launches"] += out["ba"]["gpu_launches"]
+                import bench_pipeline
+                before = _lib.launch_count()
+                out["c1_pipeline"] = bench_pipeline.run()
+                out["c1_pipeline"]["gpu_launches"] = int(_lib.launch_count() - before)
         if ba_mgpu is not None:
             out["ba"] = ba_mgpu
             out["gpu_launches"] += ba_mgpu["gpu_launches"]
