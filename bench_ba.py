@@ -217,8 +217,9 @@ def run_sharded(args, rank, world, flush):
            "value": its / (ms * 1e-3), "ms_per_solve": ms / steps, "solves": steps, "n_gpus": world,
            "config": {"workload": "C5 synthetic BAL-scale BA sharded by point: " + _name(C5),
                       "points_per_rank": prob.n_pts, "observations_per_rank": prob.n_obs,
-                      "collectives_per_trial": "all-reduce S+g_red (%.0f MB), 6 scalars, gmax; per linearisation U|g_c|cost"
-                                               % ((6000 + 48) * 6000 * 8 / 1e6)},
+                      "collectives_per_trial": "all-reduce of the packed lower block triangle of S + g_red (%.0f MB), "
+                                               "6 scalars, gmax; per linearisation U|g_c|cost"
+                                               % ((48 * 48 * 125 * 126 / 2 + 6000) * 8 / 1e6)},
            "lm_iterations_per_solve": its / steps, "cost": infos[-1]["cost"],
            "rmse_px": float(np.sqrt(2 * infos[-1]["cost"] / n5)), "status": infos[-1]["status"],
            "gpu_launches": int(_lib.launch_count() - l0)}

@@ -913,6 +913,27 @@ ba_schur_smem_kernel(const double *__restrict__ W, int nobs, const int32_t *__re
     }
 }
 
+// Multi-GPU: only the lower block triangle of S (what K10 writes and K11 reads) and the right-hand-side
+// row travel through the all-reduce. Row r < npad carries its first 48 (r / 48 + 1) entries, row npad
+// (g_red) all npad: half the bytes of the padded square.
+__host__ __device__ inline size_t s_pack_offset(int r, int npad) {
+    if (r >= npad) return (size_t)BA_NB * BA_NB * (size_t)(npad / BA_NB) * (npad / BA_NB + 1) / 2;
+    const size_t b = (size_t)r / BA_NB;
+    return (size_t)BA_NB * ((size_t)BA_NB * b * (b + 1) / 2 + ((size_t)r - BA_NB * b) * (b + 1));
+}
+
+template <bool PACK>
+__global__ void __launch_bounds__(256)
+ba_s_pack_kernel(double *__restrict__ S, size_t ld, int npad, double *__restrict__ packed) {
+    const int r = blockIdx.x;                       // 0 .. npad
+    const int len = r < npad ? BA_NB * (r / BA_NB + 1) : npad;
+    double *row = S + (size_t)r * ld, *dst = packed + s_pack_offset(r, npad);
+    for (int c = threadIdx.x; c < len; c += 256) {
+        if (PACK) dst[c] = row[c];
+        else row[c] = dst[c];
+    }
+}
+
 // ------------------------------------------------------------------------------ update (K12)
 // partial sums layout (4 doubles): [s.g, |D s|^2, |D x_new|^2, |D x_cur|^2]
 __global__ void __launch_bounds__(256)
@@ -1122,7 +1143,7 @@ struct BAPlan {
     size_t cub_bytes;
     // state
     double *cam[2], *pts[2], *camlin[2];
-    double *W, *V, *gp, *Vinv, *bp, *tp, *U, *gc, *Upart, *Dc, *Dp, *S, *Linv, *dc;
+    double *W, *V, *gp, *Vinv, *bp, *tp, *U, *gc, *Upart, *Dc, *Dp, *S, *Spack, *Linv, *dc;
     double *costpart, *updpart, *scal, *red1;
     unsigned long long *gmax;
     int *flags;       // [0] index validation, [1] schur (vinv) failure, [2] cholesky failure
@@ -1199,6 +1220,7 @@ static size_t ba_layout(BAPlan &pl, unsigned char *base, int nc, int np, int nob
     CARVE(Dc, double, D * 6 * nc);
     CARVE(Dp, double, D * 3 * np);
     CARVE(S, double, D * (pl.npad + BA_NB) * pl.ld);
+    CARVE(Spack, double, D * (s_pack_offset(pl.npad, pl.npad) + pl.npad));     // multi-GPU all-reduce staging
     CARVE(Linv, double, D * (pl.npad / BA_NB) * BA_NB * BA_NB + (size_t)(pl.npad / BA_NB + 1) * (pl.npad / BA_NB) + 64);  // + K11's block flags
     CARVE(dc, double, D * pl.npad);
     CARVE(costpart, double, D * (pl.grid_obs + 8));
@@ -1543,7 +1565,14 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
                                                              pl.S + (size_t)pl.npad * pl.ld, pl.gmax, pl.flags + 1);
             SFM_LAUNCH_CHECK();
         }
-        if ((rc = comm_allreduce_sum_f64(comm, pl.S, (size_t)(pl.npad + BA_NB) * pl.ld, st)) != SFM_OK) return rc;
+        if (comm) {
+            const size_t packed = s_pack_offset(pl.npad, pl.npad) + pl.npad;
+            ba_s_pack_kernel<true><<<pl.npad + 1, 256, 0, st>>>(pl.S, pl.ld, pl.npad, pl.Spack);
+            SFM_LAUNCH_CHECK();
+            if ((rc = comm_allreduce_sum_f64(comm, pl.Spack, packed, st)) != SFM_OK) return rc;
+            ba_s_pack_kernel<false><<<pl.npad + 1, 256, 0, st>>>(pl.S, pl.ld, pl.npad, pl.Spack);
+            SFM_LAUNCH_CHECK();
+        }
         if (update_D && (rc = comm_allreduce_max_u64(comm, pl.gmax, 1, st)) != SFM_OK) return rc;
         if ((rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st, nullptr)) != SFM_OK) return rc;
         const int nxt = cur ^ 1;
