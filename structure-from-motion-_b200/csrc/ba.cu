@@ -1574,7 +1574,22 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
             SFM_LAUNCH_CHECK();
         }
         if (update_D && (rc = comm_allreduce_max_u64(comm, pl.gmax, 1, st)) != SFM_OK) return rc;
-        if ((rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st, nullptr)) != SFM_OK) return rc;
+        static unsigned long long *d_cprof = nullptr;          // SFM_BA_CHOL_PROF=1: K11 phase profile (diagnostic)
+        static int cprof = -1;
+        if (cprof < 0) {
+            cprof = getenv("SFM_BA_CHOL_PROF") ? 1 : 0;
+            if (cprof && (cudaMalloc(&d_cprof, 8 * sizeof(unsigned long long)) != cudaSuccess ||
+                          cudaMemset(d_cprof, 0, 8 * sizeof(unsigned long long)) != cudaSuccess)) cprof = 0;
+        }
+        if ((rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st, cprof ? d_cprof : nullptr)) != SFM_OK) return rc;
+        if (cprof) {
+            unsigned long long hp[8];
+            cudaStreamSynchronize(st);
+            cudaMemcpy(hp, d_cprof, sizeof(hp), cudaMemcpyDeviceToHost);
+            cudaMemset(d_cprof, 0, sizeof(hp));
+            fprintf(stderr, "K11 phases [us]: diag %.1f trsm %.1f sync1 %.1f update %.1f sync2 %.1f back %.1f\n", hp[0] * 1e-3,
+                    hp[1] * 1e-3, hp[2] * 1e-3, hp[3] * 1e-3, hp[4] * 1e-3, hp[5] * 1e-3);
+        }
         const int nxt = cur ^ 1;
         ba_update_cams_kernel<<<1, 256, 0, st>>>(pl.cam[cur], pl.dc, pl.gc, pl.Dc, n, rank == 0, pl.cam[nxt], pl.updpart);
         SFM_LAUNCH_CHECK();
