@@ -114,7 +114,8 @@ def f_ransac_host(points1, points2, samples, threshold, want_err=False, want_all
 
 _PINNED: dict = {}
 STREAM_MIN_HYPOTHESES = 16384      # below this one sfm_f_ransac call is cheaper than chunking
-STREAM_CHUNKS = 8
+STREAM_CHUNKS = 4
+STREAM_FIRST_CHUNK = 2048
 
 
 def _pinned_i32(rows: int, cols: int) -> torch.Tensor:
@@ -132,25 +133,38 @@ def f_ransac_stream(points1, points2, threshold, n_max, chunks=STREAM_CHUNKS):
     replayed chunk by chunk into pinned memory while the GPU generates and scores the previous
     chunk (K1 + K2 per chunk, one K3 over all counts, K4 with the winner's row of F). The draws, their order and every result are the
     same as one sfm_f_ransac call over the whole stream. Returns the dict of f_ransac_host."""
-    lib, st = _lib.load(), None
-    x1x2 = np.ascontiguousarray(np.hstack([np.asarray(points1, np.float64), np.asarray(points2, np.float64)]))
-    n, h = len(x1x2), int(n_max)
-    d_x = device.to_device(x1x2)
+    lib = _lib.load()
+    p1 = np.ascontiguousarray(points1, np.float64)
+    p2 = np.ascontiguousarray(points2, np.float64)
+    n, h = len(p1), int(n_max)
+    d_x = torch.cat([device.to_device(p1), device.to_device(p2)], dim=1)     # [n,4] rows (x1,y1,x2,y2), built on device
     st = device.stream()
     r = _alloc_result(n, h, False)
     key = device.empty((1,), torch.int64)
     d_s = device.empty((h, 8), torch.int32)
     pinned = _pinned_i32(h, 8)
     host = pinned.numpy()
-    chunk = max(1, -(-h // max(1, int(chunks))))
-    for off in range(0, h, chunk):
-        c = min(chunk, h - off)
-        sampler.sample_stream(n, 8, c, out=host[off:off + c])
-        d_s[off:off + c].copy_(pinned[off:off + c], non_blocking=True)
-        _lib.check(lib.sfm_f8pt_batch(device.ptr(d_x), n, device.ptr(d_s) + 32 * off, c,
-                                      device.ptr(r.F) + 72 * off, st), "sfm_f8pt_batch")
-        _lib.check(lib.sfm_f_score_count(device.ptr(d_x), n, device.ptr(r.F) + 72 * off, c, float(threshold),
-                                         device.ptr(r.counts) + 4 * off, st), "sfm_f_score_count")
+    # chunk schedule: a small first chunk (the only one the GPU waits for), then doubling up to h / chunks
+    big = max(1, -(-h // max(1, int(chunks))))
+    sizes, c = [], min(big, STREAM_FIRST_CHUNK)
+    while sum(sizes) < h:
+        sizes.append(min(c, h - sum(sizes)))
+        c = min(big, 2 * c)
+    rep = sampler.StreamReplayer(n, 8)
+    off = 0
+    try:
+        for c in sizes:
+            rep.draw(c, host[off:off + c])
+            d_s[off:off + c].copy_(pinned[off:off + c], non_blocking=True)
+            _lib.check(lib.sfm_f8pt_batch(device.ptr(d_x), n, device.ptr(d_s) + 32 * off, c,
+                                          device.ptr(r.F) + 72 * off, st), "sfm_f8pt_batch")
+            _lib.check(lib.sfm_f_score_count(device.ptr(d_x), n, device.ptr(r.F) + 72 * off, c, float(threshold),
+                                             device.ptr(r.counts) + 4 * off, st), "sfm_f_score_count")
+            off += c
+    finally:
+        if off < h:                                    # an error mid-way: still consume the whole stream
+            rep.draw(h - off, host[off:h])
+        rep.finish()
     _lib.check(lib.sfm_argmax_first(device.ptr(r.counts), h, 0, device.ptr(r.best), device.ptr(key), st),
                "sfm_argmax_first")
     # F_best = F[winner] without a host round trip (a device-side row gather), then K4 with it

@@ -48,3 +48,43 @@ def sample_stream(n: int, k: int, count: int, out: np.ndarray | None = None) -> 
     _lib.check(rc, "sfm_mt_sample_stream")
     random.setstate((3, tuple(int(v) for v in mt) + (int(idx.value),), st[2]))
     return out
+
+
+class StreamReplayer:
+    """Chunked replay of the same stream: the generator state is read once, advanced in C chunk by chunk
+    (draw), and written back once (finish) -- the per-call getstate/setstate of sample_stream costs
+    ~0.1 ms, which matters when the chunks are pipelined against GPU work. Falls back to
+    random.sample itself when the global generator is not the stock Mersenne Twister."""
+
+    def __init__(self, n: int, k: int):
+        self.n, self.k = int(n), min(int(k), int(n))
+        inst = getattr(random, "_inst", None)
+        self.fast = (type(inst) is random.Random and getattr(random.sample, "__self__", None) is inst
+                     and self.n < 2 ** 31 and 0 < self.k <= 64)
+        if self.fast:
+            st = random.getstate()
+            self.fast = st[0] == 3 and len(st[1]) == 625
+        if self.fast:
+            self._gauss = st[2]
+            self._mt = np.array(st[1][:624], dtype=np.uint32)
+            self._idx = C.c_int32(st[1][624])
+            self._fn = _lib.load().sfm_mt_sample_stream
+
+    def draw(self, count: int, out: np.ndarray) -> np.ndarray:
+        """Fill out [count, k] (C-contiguous int32) with the next `count` index sets."""
+        if out.shape != (count, self.k) or out.dtype != np.int32 or not out.flags.c_contiguous:
+            raise ValueError("out must be a C-contiguous int32 array of shape (count, min(k, n))")
+        if count <= 0:
+            return out
+        if not self.fast:
+            out[...] = _python_stream(self.n, self.k, count)
+            return out
+        rc = self._fn(self._mt.ctypes.data, C.addressof(self._idx), self.n, self.k, count, out.ctypes.data)
+        _lib.check(rc, "sfm_mt_sample_stream")
+        return out
+
+    def finish(self) -> None:
+        """Write the advanced state back into the global generator (call exactly once)."""
+        if self.fast:
+            random.setstate((3, tuple(self._mt.tolist()) + (int(self._idx.value),), self._gauss))
+            self.fast = False

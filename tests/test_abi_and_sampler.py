@@ -53,3 +53,23 @@ def test_sample_stream_short_runs_use_python_path():
     random.seed(5)
     b = sampler.sample_stream(100, 8, 3)
     assert np.array_equal(np.array(a), b)
+
+
+def test_stream_replayer_chunks_equal_the_reference_stream():
+    """Chunked replay with one getstate/setstate: same index sets, same final generator state as
+    random.sample called once per hypothesis."""
+    from sfm_b200 import sampler
+    n, k, total = 977, 8, 5000
+    random.seed(99)
+    ref = np.array([random.sample(range(n), k) for _ in range(total)], dtype=np.int32)
+    state_ref = random.getstate()
+    random.seed(99)
+    rep = sampler.StreamReplayer(n, k)
+    out = np.empty((total, k), dtype=np.int32)
+    off = 0
+    for c in (7, 100, 1, 2048, total - 2156):
+        rep.draw(c, out[off:off + c])
+        off += c
+    rep.finish()
+    assert off == total and np.array_equal(out, ref)
+    assert random.getstate() == state_ref
