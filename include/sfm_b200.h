@@ -67,6 +67,14 @@ int sfm_f8pt_batch(const double *d_x1x2, int32_t n, const int32_t *d_sample, int
 int sfm_f_score_count(const double *d_x1x2, int32_t n, const double *d_F, int32_t h,
                       double threshold, int32_t *d_counts, void *stream);
 
+/* Diagnostics for K2. sfm_f_score_count evaluates each test in FP32 with a forward error bound and
+ * re-evaluates in FP64 whenever the bound does not separate the margin from zero, so its counts
+ * equal those of the all-FP64 kernel exposed here; sfm_f_score_fp64_tests reports (and optionally
+ * resets) how many tests took the FP64 path on this device. Host-synchronous. */
+int sfm_f_score_count_fp64(const double *d_x1x2, int32_t n, const double *d_F, int32_t h,
+                           double threshold, int32_t *d_counts, void *stream);
+int sfm_f_score_fp64_tests(uint64_t *out, int32_t reset);
+
 /* K3: first-maximum argmax (strict '>' rule of GetInliersRANSAC.py:85).
  * d_best[0] = index of the first hypothesis with the maximum count (global index =
  * local index + idx_offset), d_best[1] = that count. d_key (uint64, optional, may be null)

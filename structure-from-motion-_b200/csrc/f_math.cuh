@@ -207,6 +207,96 @@ SFM_HD bool f_is_inlier(const FMat &F, double x1, double y1, double x2, double y
     return lhs < rhs;
 }
 
+// ---- certified single-precision filter for the inlier test -------------------------------------
+// The counting kernel evaluates d = |e| (n1+n2) - 2 thr n1 n2 in FP32 together with a forward
+// error bound tol on |d - (lhs - rhs of f_is_inlier)|. When |d| > tol the sign of d IS the FP64
+// decision and the test costs FP32 issue slots only; otherwise (a few tests in 10^4 on real
+// data: |err - thr| below ~10 % of thr) the caller re-evaluates f_is_inlier in FP64. Counts are
+// therefore identical to the all-FP64 kernel by construction.
+//
+// Error model (u = 2^-24, M1/M2 = max |coordinate| of image 1 / 2 over the staged rows):
+//   |a_f - a| <= 4.01u Sa, Sa = (|F0|+|F1|) M1 + |F2|      (two input roundings + two FMAs)
+//   |e_f - e| <= 7.1u Se,  Se = M2 (Sa+Sb) + Sc
+//   |n_f - (n+eps)| <= 4.02u (Sa+Sb) + eps + 5.2u n_f       (sqrt.approx <= 2^-22 relative,
+//                                                            3e-19 covers underflow / ftz)
+// propagated through the two products; every constant below carries a factor >= 2 over the
+// bound above, which also absorbs the rounding of the bound's own evaluation and the ~1e-12
+// relative error of the FP64 form. Non-finite or out-of-range constants force the FP64 path.
+struct FCert {
+    float f0, f1, f2, f3, f4, f5, f6, f7, f8;
+    float T;      // 2 thr
+    float DeT;    // multiplies s = n1 + n2
+    float Dn12;   // multiplies |e|
+    float C0;     // constant term
+};
+
+SFM_HD float up_f32(double v) {
+    // float not below v (v >= 0): round to nearest then widen by 2^-20 relative
+    float f = (float)(v * 1.000001);
+    return f;
+}
+
+SFM_HD FCert f_cert_setup(const FMat &F, double M1, double M2, double two_thr) {
+    const double u = 5.9604644775390625e-8;  // 2^-24
+    FCert c;
+    c.f0 = (float)F.f0; c.f1 = (float)F.f1; c.f2 = (float)F.f2;
+    c.f3 = (float)F.f3; c.f4 = (float)F.f4; c.f5 = (float)F.f5;
+    c.f6 = (float)F.f6; c.f7 = (float)F.f7; c.f8 = (float)F.f8;
+    c.T = (float)two_thr;
+    double Sa = (fabs(F.f0) + fabs(F.f1)) * M1 + fabs(F.f2);
+    double Sb = (fabs(F.f3) + fabs(F.f4)) * M1 + fabs(F.f5);
+    double Sc = (fabs(F.f6) + fabs(F.f7)) * M1 + fabs(F.f8);
+    double Sp = (fabs(F.f0) + fabs(F.f3)) * M2 + fabs(F.f6);
+    double Sq = (fabs(F.f1) + fabs(F.f4)) * M2 + fabs(F.f7);
+    double Se = M2 * (Sa + Sb) + Sc;
+    double De = 16.0 * u * Se;
+    double Dn1 = 10.0 * u * (Sa + Sb) + 1e-8 + 3e-19;
+    double Dn2 = 10.0 * u * (Sp + Sq) + 1e-8 + 3e-19;
+    double T = fabs(two_thr);
+    double DeT = De + 1.01 * T * fmax(Dn1, Dn2);
+    double Dn12 = 1.01 * (Dn1 + Dn2);
+    double C0 = 1.01 * (De * (Dn1 + Dn2) + T * Dn1 * Dn2) + 1e-36;
+    // operands must stay in the range where FP32 neither overflows nor loses the bound to
+    // underflow; anything else (including NaN) always takes the FP64 path
+    bool ok = Se > 1e-12 && Se < 1e12 && M1 < 1e6 && M2 < 1e6 && T < 1e6 && two_thr >= 0.0;
+    const float inf = 3.0e38f * 10.0f;
+    c.DeT = ok ? up_f32(DeT) : inf;
+    c.Dn12 = up_f32(Dn12);
+    c.C0 = up_f32(C0);
+    return c;
+}
+
+SFM_HD float sqrt_approx_f32(float s) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(s));
+    return r;
+#else
+    return sqrtf(s);
+#endif
+}
+
+// Returns d (negative = inlier) and sets tol; the decision is certified iff |d| > tol.
+SFM_HD float f_cert_margin(const FCert &c, float x1, float y1, float x2, float y2, float &tol) {
+    float a = fmaf(c.f0, x1, fmaf(c.f1, y1, c.f2));
+    float b = fmaf(c.f3, x1, fmaf(c.f4, y1, c.f5));
+    float cc = fmaf(c.f6, x1, fmaf(c.f7, y1, c.f8));
+    float e = fabsf(fmaf(x2, a, fmaf(y2, b, cc)));
+    float p = fmaf(c.f0, x2, fmaf(c.f3, y2, c.f6));
+    float q = fmaf(c.f1, x2, fmaf(c.f4, y2, c.f7));
+    float n1 = sqrt_approx_f32(fmaf(a, a, b * b));
+    float n2 = sqrt_approx_f32(fmaf(p, p, q * q));
+    float s = n1 + n2;
+    float lhs = e * s;
+    float d = fmaf(-(c.T * n1), n2, lhs);
+    // rounding of the evaluation itself: <= 32u (lhs + rhs), and rhs = lhs - d <= lhs + |d|, so
+    // |d| > 65u lhs + (rest) implies |d| > 32u (lhs + rhs) + (rest): rhs is never formed.
+    tol = fmaf(3.874301910400391e-6f /* 65u */, lhs, c.C0);
+    tol = fmaf(c.DeT, s, tol);
+    tol = fmaf(e, c.Dn12, tol);
+    return d;
+}
+
 // The reference's expression verbatim (for the reported per-point error of the winner).
 SFM_HD double f_error_exact(const FMat &F, double x1, double y1, double x2, double y2) {
     double a = F.f0 * x1 + F.f1 * y1 + F.f2;

@@ -73,6 +73,117 @@ f_score_kernel(const double *__restrict__ x1x2, int n, const double *__restrict_
     if (hyp < h && cnt) atomicAdd(&counts[hyp], cnt);
 }
 
+// K2 with the certified FP32 filter (f_math.cuh: f_cert_margin). Same thread/hypothesis x
+// staged-chunk decomposition; shared memory holds the chunk rounded to FP32 (16 B per row). A
+// test whose FP32 margin does not clear its error bound is redone in FP64 from global memory
+// (cold path), so the counts are those of f_score_kernel bit for bit. Per test: 1 LDS.128,
+// 27 FP32-pipe + 2 MUFU instructions and 4 predicate/integer ones instead of 31 FP64.
+constexpr int K2M_GROUP = 4;
+__device__ unsigned long long g_k2_fp64_tests = 0;  // diagnostic: tests that took the cold path
+
+template <int G>
+__device__ __forceinline__ void score_group(const FCert &c, const float4 *__restrict__ rows,
+                                            const double *__restrict__ x1x2_rows,
+                                            const double *__restrict__ Frow, double two_thr,
+                                            int &cnt) {
+    unsigned unc = 0;
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+        float4 r = rows[k];
+        float tol;
+        float d = f_cert_margin(c, r.x, r.y, r.z, r.w, tol);
+        cnt += (d < -tol) ? 1 : 0;
+        unc |= (fabsf(d) > tol) ? 0u : (1u << k);
+    }
+    if (__any_sync(0xffffffffu, unc != 0)) {
+        if (unc) {
+            // opaque pointer: keeps ptxas from merging these loads with the prologue's and then
+            // holding F in FP64 registers across the hot loop
+            const double *Fr = Frow;
+            asm volatile("" : "+l"(Fr));
+            FMat F;
+            F.f0 = __ldcg(Fr + 0); F.f1 = __ldcg(Fr + 1); F.f2 = __ldcg(Fr + 2);
+            F.f3 = __ldcg(Fr + 3); F.f4 = __ldcg(Fr + 4); F.f5 = __ldcg(Fr + 5);
+            F.f6 = __ldcg(Fr + 6); F.f7 = __ldcg(Fr + 7); F.f8 = __ldcg(Fr + 8);
+            int redo = 0;
+#pragma unroll
+            for (int k = 0; k < G; ++k) {
+                if (unc & (1u << k)) {
+                    const double2 *row = reinterpret_cast<const double2 *>(x1x2_rows) + 2 * k;
+                    double2 a = __ldg(row), b = __ldg(row + 1);
+                    cnt += f_is_inlier(F, a.x, a.y, b.x, b.y, two_thr) ? 1 : 0;
+                    ++redo;
+                }
+            }
+            atomicAdd(&g_k2_fp64_tests, (unsigned long long)redo);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(K2_THREADS)
+f_score_mixed_kernel(const double *__restrict__ x1x2, int n, const double *__restrict__ Fall, int h,
+                     double two_thr, int chunk, int32_t *__restrict__ counts) {
+    extern __shared__ float4 spts32[];  // chunk rows (x1,y1,x2,y2) rounded to FP32
+    __shared__ float s_m1[K2_THREADS / 32], s_m2[K2_THREADS / 32];
+    const int p0 = blockIdx.y * chunk;
+    const int np = min(chunk, n - p0);
+    {
+        const double2 *src = reinterpret_cast<const double2 *>(x1x2) + (size_t)p0 * 2;
+        float m1 = 0.f, m2 = 0.f;
+        for (int i = threadIdx.x; i < np; i += K2_THREADS) {
+            double2 a = __ldg(src + 2 * i), b = __ldg(src + 2 * i + 1);
+            float4 r = make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);
+            spts32[i] = r;
+            // NaN coordinates: fmaxf drops them here, and they make d NaN -> FP64 path
+            m1 = fmaxf(m1, fmaxf(fabsf(r.x), fabsf(r.y)));
+            m2 = fmaxf(m2, fmaxf(fabsf(r.z), fabsf(r.w)));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, o));
+            m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+        }
+        if ((threadIdx.x & 31) == 0) {
+            s_m1[threadIdx.x >> 5] = m1;
+            s_m2[threadIdx.x >> 5] = m2;
+        }
+    }
+    const int hyp = blockIdx.x * K2_THREADS + threadIdx.x;
+    const double *Frow = Fall + (size_t)min(hyp, h - 1) * 9;
+    __syncthreads();
+    FCert c;
+    {
+        float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+        for (int w = 0; w < K2_THREADS / 32; ++w) {
+            m1 = fmaxf(m1, s_m1[w]);
+            m2 = fmaxf(m2, s_m2[w]);
+        }
+        FMat F;
+        F.f0 = __ldg(Frow + 0); F.f1 = __ldg(Frow + 1); F.f2 = __ldg(Frow + 2);
+        F.f3 = __ldg(Frow + 3); F.f4 = __ldg(Frow + 4); F.f5 = __ldg(Frow + 5);
+        F.f6 = __ldg(Frow + 6); F.f7 = __ldg(Frow + 7); F.f8 = __ldg(Frow + 8);
+        // the FP32 rounding of a coordinate can exceed the FP64 value by one part in 2^24
+        c = f_cert_setup(F, (double)m1 * 1.0000002, (double)m2 * 1.0000002, two_thr);
+        // pin the FP32 constants in registers: ptxas otherwise keeps F in FP64 registers and
+        // re-converts inside the loop (F2F shares the quarter-rate pipe with the two MUFU.SQRT).
+        // z is 0 at run time (chunk > 0) but not at compile time.
+        const int z = chunk >> 31;
+#define SFM_PIN(x) x = __int_as_float(__float_as_int(x) | z)
+        SFM_PIN(c.f0); SFM_PIN(c.f1); SFM_PIN(c.f2); SFM_PIN(c.f3); SFM_PIN(c.f4);
+        SFM_PIN(c.f5); SFM_PIN(c.f6); SFM_PIN(c.f7); SFM_PIN(c.f8); SFM_PIN(c.T);
+        SFM_PIN(c.DeT); SFM_PIN(c.Dn12); SFM_PIN(c.C0);
+#undef SFM_PIN
+    }
+    int cnt = 0;
+    const double *grow = x1x2 + (size_t)p0 * 4;
+    int i = 0;
+    for (; i + K2M_GROUP <= np; i += K2M_GROUP)
+        score_group<K2M_GROUP>(c, spts32 + i, grow + (size_t)i * 4, Frow, two_thr, cnt);
+    for (; i < np; ++i) score_group<1>(c, spts32 + i, grow + (size_t)i * 4, Frow, two_thr, cnt);
+    if (hyp < h && cnt) atomicAdd(&counts[hyp], cnt);
+}
+
 // ------------------------------------------------------------------------------------ K3
 // key = (count << 32) | (0xFFFFFFFF - global index): max(key) = largest count, and among equal
 // counts the LOWEST index, which is the reference's strict '>' update rule.
@@ -157,14 +268,21 @@ extern "C" int sfm_f8pt_batch(const double *d_x1x2, int32_t n, const int32_t *d_
     return SFM_OK;
 }
 
-extern "C" int sfm_f_score_count(const double *d_x1x2, int32_t n, const double *d_F, int32_t h,
-                                 double threshold, int32_t *d_counts, void *stream) {
+static int f_score_launch(const double *d_x1x2, int32_t n, const double *d_F, int32_t h,
+                          double threshold, int32_t *d_counts, void *stream, bool all_fp64) {
     if (!d_x1x2 || !d_F || !d_counts || n < 0 || h < 0) return SFM_E_INVALID;
     if (h == 0) return SFM_OK;
     cudaStream_t st = as_stream(stream);
     SFM_CUDA_TRY(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)h, st));
     if (n == 0) return SFM_OK;
     int chunk = pick_chunk(n, h);
+    dim3 grid(ceil_div(h, K2_THREADS), ceil_div(n, chunk));
+    if (!all_fp64) {
+        f_score_mixed_kernel<<<grid, K2_THREADS, sizeof(float4) * (size_t)chunk, st>>>(
+            d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);
+        SFM_LAUNCH_CHECK();
+        return SFM_OK;
+    }
     size_t smem = (size_t)chunk * 32;
     static bool attr_set = false;
     if (!attr_set) {
@@ -172,10 +290,34 @@ extern "C" int sfm_f_score_count(const double *d_x1x2, int32_t n, const double *
                                           1024 * 32));
         attr_set = true;
     }
-    dim3 grid(ceil_div(h, K2_THREADS), ceil_div(n, chunk));
     f_score_kernel<<<grid, K2_THREADS, smem, st>>>(d_x1x2, n, d_F, h, 2.0 * threshold, chunk,
                                                    d_counts);
     SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+extern "C" int sfm_f_score_count(const double *d_x1x2, int32_t n, const double *d_F, int32_t h,
+                                 double threshold, int32_t *d_counts, void *stream) {
+    static const bool all_fp64 = getenv("SFM_F_SCORE_F64") != nullptr;  // development switch
+    return f_score_launch(d_x1x2, n, d_F, h, threshold, d_counts, stream, all_fp64);
+}
+
+// Diagnostics: the all-FP64 scoring kernel (what the certified filter must reproduce), and the
+// number of point-hypothesis tests the filter handed to the FP64 path since the last reset.
+extern "C" int sfm_f_score_count_fp64(const double *d_x1x2, int32_t n, const double *d_F, int32_t h,
+                                      double threshold, int32_t *d_counts, void *stream) {
+    return f_score_launch(d_x1x2, n, d_F, h, threshold, d_counts, stream, true);
+}
+
+extern "C" int sfm_f_score_fp64_tests(uint64_t *out, int32_t reset) {
+    unsigned long long v = 0;
+    SFM_CUDA_TRY(cudaDeviceSynchronize());
+    SFM_CUDA_TRY(cudaMemcpyFromSymbol(&v, g_k2_fp64_tests, sizeof(v)));
+    if (out) *out = v;
+    if (reset) {
+        v = 0;
+        SFM_CUDA_TRY(cudaMemcpyToSymbol(g_k2_fp64_tests, &v, sizeof(v)));
+    }
     return SFM_OK;
 }
 

@@ -180,3 +180,42 @@ def test_fransac_stream_equals_single_call(cuda_device):
     assert h >= ransac.STREAM_MIN_HYPOTHESES
     assert np.array_equal(inl, np.where(ref["mask"])[0]) and np.array_equal(F, ref["F_best"])
     assert random.getstate() == state_after
+
+
+def test_certified_fp32_scoring_equals_fp64_kernel(cuda_device):
+    """K2 decides each test in FP32 under a forward error bound and falls back to FP64 inside the
+    band the bound cannot separate; its counts must equal the all-FP64 kernel's exactly — on the
+    C2 scene, on P3Data-like integer coordinates, and on non-finite / badly scaled hypotheses."""
+    import ctypes as C
+    import torch
+    from sfm_b200 import _lib, scenes, sampler, device
+    lib = _lib.load()
+    sc = scenes.two_view()
+    n, h = len(sc["x1"]), 6000
+    random.seed(99)
+    samples = sampler.sample_stream(n, 8, h)
+    x = np.hstack([sc["x1"], sc["x2"]])
+    cases = [(x, 0.06), (x, 1.0), (np.floor(x), 0.06), (x * 1e-3, 1e-4), (x[:1237], 0.5), (x[:9], 0.5)]
+    v = C.c_uint64(0)
+    for rows, thr in cases:
+        m = len(rows)
+        d_x = device.to_device(np.ascontiguousarray(rows))
+        d_s = device.to_device(samples % m if m < n else samples, np.int32)
+        d_F = torch.empty((h, 9), dtype=torch.float64, device="cuda")
+        assert lib.sfm_f8pt_batch(d_x.data_ptr(), m, d_s.data_ptr(), h, d_F.data_ptr(), None) == 0
+        variants = [d_F]
+        if m == n and thr == 0.06:
+            bad = d_F.clone()
+            bad[0, 3] = float("nan"); bad[1, 8] = float("inf"); bad[2] = 0.0
+            bad[3] *= 1e25; bad[4] *= 1e-25; bad[5] *= -1e8
+            variants.append(bad)
+        for F in variants:
+            a = torch.empty(h, dtype=torch.int32, device="cuda")
+            b = torch.empty(h, dtype=torch.int32, device="cuda")
+            lib.sfm_f_score_fp64_tests(C.byref(v), 1)
+            assert lib.sfm_f_score_count(d_x.data_ptr(), m, F.data_ptr(), h, thr, a.data_ptr(), None) == 0
+            lib.sfm_f_score_fp64_tests(C.byref(v), 1)
+            assert lib.sfm_f_score_count_fp64(d_x.data_ptr(), m, F.data_ptr(), h, thr, b.data_ptr(), None) == 0
+            assert torch.equal(a, b), (m, thr, int((a != b).sum()))
+            if F is d_F and m == n:
+                assert v.value < 0.02 * m * h           # the filter decides almost everything
