@@ -47,6 +47,32 @@ def test_sample_stream_matches_cpython():
         assert after_a == after_b, "global generator state must advance exactly like the reference"
 
 
+def test_sample_stream_two_pass_replay_edges():
+    """The bulk replay (csrc/mt_sample.cpp: compaction of accepted words, rows of k, slow path for rows
+    with a repeated value, rows carried across 624-word generations): n a power of two and one below,
+    n barely above CPython's set threshold (many repeats), k other than 4 / 8, every starting offset
+    class inside a generation, counts that end a call in the middle of a generation."""
+    for n, k in [(65536, 8), (65535, 8), (86, 8), (100, 8), (22, 4), (23, 3), (40, 5), (200, 6), (1000, 20),
+                 (500, 64), (64, 64)]:
+        random.seed(n * 131 + k)
+        a = np.array([random.sample(range(n), k) for _ in range(1500)])
+        after_a = random.random()
+        random.seed(n * 131 + k)
+        b = sampler.sample_stream(n, k, 1500)
+        assert np.array_equal(a, b), (n, k)
+        assert after_a == random.random(), (n, k)
+    for off in range(0, 700, 37):
+        for cnt in (16, 17, 77, 500):
+            random.seed(5)
+            [random.getrandbits(32) for _ in range(off)]
+            a = np.array([random.sample(range(50000), 8) for _ in range(cnt)])
+            after_a = random.random()
+            random.seed(5)
+            [random.getrandbits(32) for _ in range(off)]
+            b = sampler.sample_stream(50000, 8, cnt)
+            assert np.array_equal(a, b) and after_a == random.random(), (off, cnt)
+
+
 def test_sample_stream_short_runs_use_python_path():
     random.seed(5)
     a = [random.sample(range(100), 8) for _ in range(3)]
