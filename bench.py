@@ -44,24 +44,67 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
 
 
+def _ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` at the bench shape, from the
+    committed ncu --set full capture (profiles/r01_ncu_traffic.json, written by tools/ncu_traffic.py)."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_ncu_traffic.json")) as f:
+            return float(json.load(f)[kernel]["dram_bytes"])
+    except Exception:
+        return None
+
+
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled DURING the timed region."""
+    """SM clock and throttle reasons sampled DURING the timed regions (every ~10 ms through NVML; nvidia-smi
+    every 0.2 s if the NVML binding is unavailable)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index=0):
         self.samples, self.stop_evt, self.index = [], threading.Event(), index
+        self.sm_max, self.how = None, "nvidia-smi"
         self.thread = threading.Thread(target=self._run, daemon=True)
 
+    def _run_nvml(self):
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(self._physical_index())
+        self.sm_max = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+        bits = [nv.nvmlClocksThrottleReasonHwSlowdown, nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                nv.nvmlClocksThrottleReasonSwThermalSlowdown, nv.nvmlClocksThrottleReasonSwPowerCap]
+        self.how = "nvml"
+        while not self.stop_evt.is_set():
+            mhz = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+            r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+            self.samples.append((mhz, [bool(r & b) for b in bits]))
+            self.stop_evt.wait(0.01)
+
+    def _physical_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        ids = [v for v in vis.split(",") if v.strip()]
+        if ids and all(v.strip().isdigit() for v in ids) and self.index < len(ids):
+            return int(ids[self.index])
+        return self.index
+
     def _run(self):
+        try:
+            self._run_nvml()
+            return
+        except Exception:
+            self.how = "nvidia-smi"
         while not self.stop_evt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                out = subprocess.run(["nvidia-smi", f"--id={self._physical_index()}", f"--query-gpu={self.Q}",
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True,
                                      timeout=5).stdout.strip()
                 if out:
-                    self.samples.append([c.strip() for c in out.splitlines()[0].split(",")])
+                    c = [v.strip() for v in out.splitlines()[0].split(",")]
+                    if c[0].replace(".", "").isdigit():
+                        if c[1].replace(".", "").isdigit():
+                            self.sm_max = float(c[1])
+                        self.samples.append((float(c[0]), [v.lower().startswith("active") for v in c[3:7]]))
             except Exception:
                 pass
             self.stop_evt.wait(0.2)
@@ -76,13 +119,12 @@ class ClockSampler:
 
     def summary(self):
         if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(s[3 + i].lower().startswith("active") for s in self.samples)]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
-                "sm_max_mhz": float(self.samples[0][1]) if self.samples[0][1].replace(".", "").isdigit() else None,
-                "reasons": reasons, "samples": len(self.samples)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock query unavailable"]}
+        sm = sorted(s[0] for s in self.samples)
+        reasons = [n for i, n in enumerate(self.NAMES) if any(s[1][i] for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_min_mhz": sm[0], "sm_max_mhz": self.sm_max,
+                "reasons": reasons, "samples": len(self.samples), "how": self.how,
+                "covers": "every timed region of this line (F-RANSAC steps, K2 alone, end-to-end, BA)"}
 
 
 def make_inputs(n_hyp_total):
@@ -182,14 +224,14 @@ def run_ours(args, rank, world):
     barrier()
     launches0 = _lib.launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    with ClockSampler(local) as clocks:
-        barrier()
-        for a, b in ev:
-            flush.zero_()                      # L2 flush between timed iterations (outside the events)
-            a.record()
-            r = step()
-            b.record()
-        barrier()
+    clocks = ClockSampler(local).__enter__()   # stopped right before the line is printed
+    barrier()
+    for a, b in ev:
+        flush.zero_()                      # L2 flush between timed iterations (outside the events)
+        a.record()
+        r = step()
+        b.record()
+    barrier()
     launches = _lib.launch_count() - launches0
     ms = sum(a.elapsed_time(b) for a, b in ev)
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
@@ -212,19 +254,28 @@ def run_ours(args, rank, world):
     peaks, peak_src = measured_peaks()
     alg_bytes = (32.0 * N_PTS + 76.0) * N_HYP
     achieved = alg_bytes / (k2_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "f_score_kernel (K2)", "achieved": achieved,
+    tests = float(N_PTS) * N_HYP
+    fma_peak = 148 * 128 * 1.965e9          # FP32 FMA lanes x clock: 119-125 of 128 per clock and SM measured
+    roofline = {"bound": "hbm", "kernel": "f_score_packed_kernel (K2)", "achieved": achieved,
                 "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                "traffic": None, "peak_source": peak_src, "kernel_ms": k2_ms,
+                "traffic": _ncu_traffic("f_score_packed_kernel"), "peak_source": peak_src, "kernel_ms": k2_ms,
                 "algorithmic_bytes_per_launch": alg_bytes,
-                "note": "algorithmic bytes = (32 B x N + 76 B) per hypothesis (SURVEY 8d); the 1.6 MB "
-                        "correspondence set is SMEM/L2 resident, so the physical limiter is the FP64 pipe: "
-                        "see fp64_pipe",
-                "fp64_pipe": {"fp64_instr_per_test": 31, "tests_per_launch": float(N_PTS) * N_HYP,
-                              "achieved_tinstr_s": 31.0 * N_PTS * N_HYP / (k2_ms * 1e-3) / 1e12,
-                              # one FP64 warp instruction per 2 cycles and scheduler (measured,
-                              # profiles/r01_ubench_b200.txt): 148 SMs x 4 x 16 lanes x 1.965 GHz
-                              "peak_tinstr_s": 148 * 4 * 16 * 1.965e9 / 1e12,
-                              "frac": 31.0 * N_PTS * N_HYP / (k2_ms * 1e-3) / (148 * 4 * 16 * 1.965e9)}}
+                "note": "algorithmic bytes = (32 B x N + 76 B) per hypothesis (SURVEY 8d): what a kernel without "
+                        "on-chip reuse would stream. The 1.6 MB correspondence set is staged in shared memory "
+                        "and re-read by every hypothesis tile, so frac > 1 is the on-chip reuse factor, not an "
+                        "HBM fraction (traffic = DRAM bytes per launch from the ncu capture under profiles/); the physical "
+                        "limiter is the "
+                        "FP32 FMA pipe: see fp32_pipe",
+                "fp32_pipe": {"fma_lane_ops_per_test": 23,
+                              "what": "certified FP32 filter on packed FFMA2/FMUL2/FADD2: 23 packed instructions "
+                                      "per pair of tests = 23 FMA-lane operations per test, + 2 MUFU.SQRT; 2e-4 of "
+                                      "the tests are redone in FP64",
+                              "tests_per_launch": tests,
+                              "achieved_tlaneops_s": 23.0 * tests / (k2_ms * 1e-3) / 1e12,
+                              "peak_tlaneops_s": fma_peak / 1e12,
+                              "frac": 23.0 * tests / (k2_ms * 1e-3) / fma_peak,
+                              "peak_source": "148 SMs x 128 FP32 lanes x 1.965 GHz; profiles/r01_ubench_fp32_b200.txt "
+                                             "measures 119 (FFMA) and 125 (FFMA2, broadcast operands) of 128"}}
 
     # end to end through the drop-in signature: host numpy in, host numpy out, RNG replay, H2D, D2H
     index = np.arange(N_PTS)
@@ -275,6 +326,8 @@ def run_ours(args, rank, world):
         if ba_mgpu is not None:
             out["ba"] = ba_mgpu
             out["gpu_launches"] += ba_mgpu["gpu_launches"]
+        clocks.__exit__()
+        out["clocks"] = clocks.summary()
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -1,7 +1,9 @@
 // f_ransac.cu -- K1..K4 of the F-matrix RANSAC path for sm_100a.
 //
 //   K1 f8pt_kernel        EstimateFundamentalMatrix.py:30-78 for every sampled 8-tuple
-//   K2 f_score_kernel     GetInliersRANSAC.py:67-82: inlier count of every hypothesis
+//   K2 f_score_packed_kernel GetInliersRANSAC.py:67-82: inlier count of every hypothesis
+//      (f_score_kernel = the all-FP64 form it must reproduce; f_score_mixed_kernel = the scalar
+//       FP32 filter it replaced, kept behind SFM_F_SCORE_SCALAR32 for comparison)
 //   K3 argmax_first_kernel GetInliersRANSAC.py:85: first hypothesis with the maximum count
 //   K4 f_mask_kernel      GetInliersRANSAC.py:81,87 for the winner
 //
@@ -9,11 +11,13 @@
 // samples [h,8] i32; hypotheses [h,9] f64; counts [h] i32.
 //
 // K2 is the hot kernel: h x n point-hypothesis tests. One thread owns one hypothesis (its F
-// stays in 18 registers), a block stages a chunk of correspondences in shared memory with
-// 16-byte loads and every warp reads them back as broadcasts, so the inner loop is pure FP64
-// pipe work (~37 FP64 instructions per test, no divisions, one MUFU per square root). The grid
-// is (hypothesis tiles) x (point chunks); partial counts are merged with integer atomics, so
-// the result is order-independent and bit-reproducible.
+// stays in registers), a block stages a chunk of correspondences in shared memory and every
+// warp reads them back as broadcasts, so the inner loop is pure arithmetic-pipe work: 31 FP64
+// instructions per test in f_score_kernel; in the shipped kernel a certified FP32 filter on the
+// packed FP32 pipe (11.5 FFMA2-class + 2 MUFU per test) with an FP64 redo of the ~2 tests in
+// 10^4 it cannot decide, which gives the FP64 kernel's counts bit for bit. The grid is
+// (hypothesis tiles) x (point chunks); partial counts are merged with integer atomics, so the
+// result is order-independent and bit-reproducible.
 #include "f_math.cuh"
 
 namespace sfm {
@@ -184,6 +188,188 @@ f_score_mixed_kernel(const double *__restrict__ x1x2, int n, const double *__res
     if (hyp < h && cnt) atomicAdd(&counts[hyp], cnt);
 }
 
+// K2 on Blackwell's packed FP32 pipe (FFMA2 / FMUL2 / FADD2 = fma|mul|add.rn.f32x2, sm_100+): the
+// certified filter above for TWO correspondences per instruction. One thread still owns one
+// hypothesis; shared memory holds the chunk pair-interleaved, (x1a,x1b,y1a,y1b),(x2a,x2b,y2a,y2b),
+// so one LDS.128 lands each operand pair in an aligned 64-bit register pair, and the nine F
+// entries and the bound's constants sit in registers duplicated in both halves. Every packed
+// operation rounds each half exactly like the scalar fmaf/mul/add of f_cert_margin, so d and tol
+// are bit-identical to the scalar filter and the same certification argument holds; only the
+// square roots, |e| and the comparisons stay scalar. Per pair of tests: 2 LDS.128, 23 packed
+// FP32, 4 MUFU, 2 LOP and ~8 predicate/integer instructions (20 issue slots per test instead
+// of 34).
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk2(float lo, float hi) {
+    u64 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk2(u64 v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+    u64 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) {
+    u64 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ u64 add2(u64 a, u64 b) {
+    u64 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+struct FCert2 {
+    u64 f0, f1, f2, f3, f4, f5, f6, f7, f8;
+    u64 nT;                     // -2 thr
+    u64 DeT, Dn12, C0, U65;     // f_cert_margin's bound constants, 65u
+};
+
+template <int PG>  // pairs per uncertainty check
+__device__ __forceinline__ void score_pairs(const FCert2 &c, const float4 *__restrict__ rows,
+                                            const double *__restrict__ x1x2_rows,
+                                            const double *__restrict__ Frow, double two_thr,
+                                            int &cnt) {
+    unsigned unc = 0;
+#pragma unroll
+    for (int k = 0; k < PG; ++k) {
+        float4 A = rows[2 * k], B = rows[2 * k + 1];
+        u64 x1 = pk2(A.x, A.y), y1 = pk2(A.z, A.w), x2 = pk2(B.x, B.y), y2 = pk2(B.z, B.w);
+        u64 a = fma2(c.f0, x1, fma2(c.f1, y1, c.f2));
+        u64 b = fma2(c.f3, x1, fma2(c.f4, y1, c.f5));
+        u64 cc = fma2(c.f6, x1, fma2(c.f7, y1, c.f8));
+        u64 e = fma2(x2, a, fma2(y2, b, cc));
+        u64 p = fma2(c.f0, x2, fma2(c.f3, y2, c.f6));
+        u64 q = fma2(c.f1, x2, fma2(c.f4, y2, c.f7));
+        u64 q1 = fma2(a, a, mul2(b, b)), q2 = fma2(p, p, mul2(q, q));
+        float q1l, q1h, q2l, q2h, el, eh;
+        upk2(q1, q1l, q1h);
+        upk2(q2, q2l, q2h);
+        upk2(e, el, eh);
+        u64 n1 = pk2(sqrt_approx_f32(q1l), sqrt_approx_f32(q1h));
+        u64 n2 = pk2(sqrt_approx_f32(q2l), sqrt_approx_f32(q2h));
+        u64 ea = pk2(fabsf(el), fabsf(eh));
+        u64 s = add2(n1, n2);
+        u64 lhs = mul2(ea, s);
+        u64 d = fma2(mul2(c.nT, n1), n2, lhs);
+        u64 tol = fma2(c.U65, lhs, c.C0);
+        tol = fma2(c.DeT, s, tol);
+        tol = fma2(ea, c.Dn12, tol);
+        float d0, d1, t0, t1;
+        upk2(d, d0, d1);
+        upk2(tol, t0, t1);
+        cnt += (d0 < -t0) ? 1 : 0;
+        cnt += (d1 < -t1) ? 1 : 0;
+        unc |= (fabsf(d0) > t0) ? 0u : (1u << (2 * k));
+        unc |= (fabsf(d1) > t1) ? 0u : (2u << (2 * k));
+    }
+    if (__any_sync(0xffffffffu, unc != 0)) {
+        if (unc) {
+            const double *Fr = Frow;  // opaque, see score_group
+            asm volatile("" : "+l"(Fr));
+            FMat F;
+            F.f0 = __ldcg(Fr + 0); F.f1 = __ldcg(Fr + 1); F.f2 = __ldcg(Fr + 2);
+            F.f3 = __ldcg(Fr + 3); F.f4 = __ldcg(Fr + 4); F.f5 = __ldcg(Fr + 5);
+            F.f6 = __ldcg(Fr + 6); F.f7 = __ldcg(Fr + 7); F.f8 = __ldcg(Fr + 8);
+            int redo = 0;
+#pragma unroll
+            for (int t = 0; t < 2 * PG; ++t) {
+                if (unc & (1u << t)) {
+                    const double2 *row = reinterpret_cast<const double2 *>(x1x2_rows) + 2 * t;
+                    double2 a = __ldg(row), b = __ldg(row + 1);
+                    cnt += f_is_inlier(F, a.x, a.y, b.x, b.y, two_thr) ? 1 : 0;
+                    ++redo;
+                }
+            }
+            atomicAdd(&g_k2_fp64_tests, (unsigned long long)redo);
+        }
+    }
+}
+
+// Two pairs per uncertainty vote and 4 CTAs per SM: measured best of {1,2,4} pairs x {4,5,6} CTAs
+// (4.76-5.45 ms at C2; more CTAs per SM spill).
+constexpr int K2P_PAIRS = 2;
+
+__global__ void __launch_bounds__(K2_THREADS, 4)
+f_score_packed_kernel(const double *__restrict__ x1x2, int n, const double *__restrict__ Fall, int h,
+                      double two_thr, int chunk, int32_t *__restrict__ counts) {
+    extern __shared__ float4 spair[];  // chunk/2 pairs x 2 float4, pair-interleaved FP32 rows
+    __shared__ float s_m1[K2_THREADS / 32], s_m2[K2_THREADS / 32];
+    const int p0 = blockIdx.y * chunk;  // even: chunk is
+    const int np = min(chunk, n - p0);
+    {
+        const double2 *src = reinterpret_cast<const double2 *>(x1x2) + (size_t)p0 * 2;
+        float *sf = reinterpret_cast<float *>(spair);
+        float m1 = 0.f, m2 = 0.f;
+        for (int i = threadIdx.x; i < np; i += K2_THREADS) {
+            double2 a = __ldg(src + 2 * i), b = __ldg(src + 2 * i + 1);
+            float4 r = make_float4((float)a.x, (float)a.y, (float)b.x, (float)b.y);
+            float *dst = sf + (i >> 1) * 8 + (i & 1);
+            dst[0] = r.x; dst[2] = r.y; dst[4] = r.z; dst[6] = r.w;
+            m1 = fmaxf(m1, fmaxf(fabsf(r.x), fabsf(r.y)));
+            m2 = fmaxf(m2, fmaxf(fabsf(r.z), fabsf(r.w)));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, o));
+            m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+        }
+        if ((threadIdx.x & 31) == 0) {
+            s_m1[threadIdx.x >> 5] = m1;
+            s_m2[threadIdx.x >> 5] = m2;
+        }
+    }
+    const int hyp = blockIdx.x * K2_THREADS + threadIdx.x;
+    const double *Frow = Fall + (size_t)min(hyp, h - 1) * 9;
+    __syncthreads();
+    FCert c;
+    {
+        float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+        for (int w = 0; w < K2_THREADS / 32; ++w) {
+            m1 = fmaxf(m1, s_m1[w]);
+            m2 = fmaxf(m2, s_m2[w]);
+        }
+        FMat F;
+        F.f0 = __ldg(Frow + 0); F.f1 = __ldg(Frow + 1); F.f2 = __ldg(Frow + 2);
+        F.f3 = __ldg(Frow + 3); F.f4 = __ldg(Frow + 4); F.f5 = __ldg(Frow + 5);
+        F.f6 = __ldg(Frow + 6); F.f7 = __ldg(Frow + 7); F.f8 = __ldg(Frow + 8);
+        c = f_cert_setup(F, (double)m1 * 1.0000002, (double)m2 * 1.0000002, two_thr);
+    }
+    FCert2 c2;
+    {
+        // runtime-opaque zero: keeps ptxas from rematerialising the packed constants from the
+        // FP64 F inside the loop (see f_score_mixed_kernel)
+        const int z = chunk >> 31;
+#define SFM_DUP(x) pk2(__int_as_float(__float_as_int(x) | z), __int_as_float(__float_as_int(x) | z))
+        c2.f0 = SFM_DUP(c.f0); c2.f1 = SFM_DUP(c.f1); c2.f2 = SFM_DUP(c.f2);
+        c2.f3 = SFM_DUP(c.f3); c2.f4 = SFM_DUP(c.f4); c2.f5 = SFM_DUP(c.f5);
+        c2.f6 = SFM_DUP(c.f6); c2.f7 = SFM_DUP(c.f7); c2.f8 = SFM_DUP(c.f8);
+        float nT = -c.T, u65 = 3.874301910400391e-6f;
+        c2.nT = SFM_DUP(nT); c2.DeT = SFM_DUP(c.DeT); c2.Dn12 = SFM_DUP(c.Dn12);
+        c2.C0 = SFM_DUP(c.C0); c2.U65 = SFM_DUP(u65);
+#undef SFM_DUP
+    }
+    int cnt = 0;
+    const double *grow = x1x2 + (size_t)p0 * 4;
+    const int npair = np >> 1;
+    int j = 0;
+    for (; j + K2P_PAIRS <= npair; j += K2P_PAIRS)
+        score_pairs<K2P_PAIRS>(c2, spair + 2 * j, grow + (size_t)j * 8, Frow, two_thr, cnt);
+    for (; j < npair; ++j) score_pairs<1>(c2, spair + 2 * j, grow + (size_t)j * 8, Frow, two_thr, cnt);
+    if (np & 1) {
+        // odd tail of the last chunk: the scalar filter on lane 0 of the last pair
+        float4 A = spair[2 * npair], B = spair[2 * npair + 1];
+        float4 r = make_float4(A.x, A.z, B.x, B.z);
+        score_group<1>(c, &r, grow + (size_t)(np - 1) * 4, Frow, two_thr, cnt);
+    }
+    if (hyp < h && cnt) atomicAdd(&counts[hyp], cnt);
+}
+
 // ------------------------------------------------------------------------------------ K3
 // key = (count << 32) | (0xFFFFFFFF - global index): max(key) = largest count, and among equal
 // counts the LOWEST index, which is the reference's strict '>' update rule.
@@ -278,8 +464,14 @@ static int f_score_launch(const double *d_x1x2, int32_t n, const double *d_F, in
     int chunk = pick_chunk(n, h);
     dim3 grid(ceil_div(h, K2_THREADS), ceil_div(n, chunk));
     if (!all_fp64) {
-        f_score_mixed_kernel<<<grid, K2_THREADS, sizeof(float4) * (size_t)chunk, st>>>(
-            d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);
+        // development switch: the scalar-FP32 filter the packed kernel replaced
+        static const bool scalar32 = getenv("SFM_F_SCORE_SCALAR32") != nullptr;
+        if (scalar32)
+            f_score_mixed_kernel<<<grid, K2_THREADS, sizeof(float4) * (size_t)chunk, st>>>(
+                d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);
+        else
+            f_score_packed_kernel<<<grid, K2_THREADS, sizeof(float4) * (size_t)chunk, st>>>(
+                d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);
         SFM_LAUNCH_CHECK();
         return SFM_OK;
     }

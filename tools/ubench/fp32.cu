@@ -26,6 +26,11 @@ constexpr int ITER = 4096;
 // mode 3: mode 1 + one MUFU.SQRT per 6 FFMA2
 // mode 4: mode 0 + one FSETP/IADD pair per 8 FFMA
 // mode 5: mode 1 + one FSETP/IADD pair per 4 FFMA2
+// mode 6: 2 FFMA2 chains + 4 scalar FFMA chains interleaved (same flops as mode 0): do the packed
+//         and the scalar instructions share one pipe or run side by side?
+// mode 7: 4 FFMA2 chains whose multiplier/addend have equal halves (ptxas emits the .F32
+//         broadcast operand form, as in f_score_packed_kernel)
+// mode 8: 3 FFMA2 chains + 2 scalar FFMA chains (same flops as mode 0)
 template <int MODE>
 __global__ void __launch_bounds__(256) k(float *out, float seed) {
     float x[8];
@@ -38,7 +43,32 @@ __global__ void __launch_bounds__(256) k(float *out, float seed) {
     float m = seed + 2.f;
     int cnt = 0;
     for (int it = 0; it < ITER; ++it) {
-        if (MODE == 0 || MODE == 2 || MODE == 4) {
+        if (MODE == 6) {
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    y[i] = ffma2(y[i], (i & 1) ? b2 : c2, (i & 1) ? c2 : b2);
+                    x[4 + 2 * i] = fmaf(x[4 + 2 * i], b, c);
+                    x[5 + 2 * i] = fmaf(x[5 + 2 * i], d, b);
+                }
+            }
+        } else if (MODE == 8) {
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+#pragma unroll
+                for (int i = 0; i < 3; ++i) y[i] = ffma2(y[i], (i & 1) ? b2 : c2, (i & 1) ? c2 : b2);
+                x[6] = fmaf(x[6], b, c);
+                x[7] = fmaf(x[7], d, b);
+            }
+        } else if (MODE == 7) {
+            float2 bb = make_float2(b, b), cc2 = make_float2(c, c);
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) y[i] = ffma2(y[i], bb, cc2);
+            }
+        } else if (MODE == 0 || MODE == 2 || MODE == 4) {
 #pragma unroll
             for (int r = 0; r < 3; ++r) {
 #pragma unroll
@@ -94,5 +124,8 @@ int main() {
     run<3>("FFMA2 x12 + 2 MUFU.SQRT", d);
     run<4>("FFMA x24 + 3 (FSETP+IADD)", d);
     run<5>("FFMA2 x12 + 3 (FSETP+IADD)", d);
+    run<6>("FFMA2 x6 + FFMA x12 interleaved", d);
+    run<8>("FFMA2 x9 + FFMA x6 interleaved", d);
+    run<7>("FFMA2 x12, broadcast .F32 operands", d);
     return 0;
 }
