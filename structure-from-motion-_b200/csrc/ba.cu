@@ -241,6 +241,17 @@ ba_point_pass_kernel(KParam K, const double *__restrict__ camlin, int nc, const 
 }
 
 // K8. Same traversal as K9p, residual only. r_out (may be null): [nobs,2] interleaved residuals.
+// The pass moves 48 B per observation and computes almost nothing, so it is written around the
+// memory pipeline: shared memory holds only the projective part of each camera record (M, K t:
+// 12 of the 22 doubles, padded to 14: 112 KB at 1,000 cameras), the index/observation loads of the first two
+// rounds are requested BEFORE the table is staged (the staging would otherwise run with HBM idle),
+// and inside the loop the indices run two rounds and the point gather one round ahead of the
+// arithmetic, as in K9p.
+constexpr int K8_CAM_DOUBLES = 12;
+// shared-memory record stride: 7 x 16 B. An odd number of 16-byte words spreads the per-lane
+// record gather (LDS.128 at 16 B x (7 c + j)) over all eight 4-bank groups; at the natural
+// 6-word stride 6c mod 8 only reaches the even groups and the gather takes twice the wavefronts.
+constexpr int K8_CAM_STRIDE = 14;
 template <bool SMEM_CAMS, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
 ba_cost_kernel(const double *__restrict__ camlin, int nc, const double *__restrict__ pts,
@@ -249,37 +260,47 @@ ba_cost_kernel(const double *__restrict__ camlin, int nc, const double *__restri
                double2 *__restrict__ r_out) {
     extern __shared__ __align__(16) double scam[];
     __shared__ double sred[32];
+    const int stride = gridDim.x * THREADS;
+    int o = blockIdx.x * THREADS + threadIdx.x;
+    int c_cur = 0, p_cur = 0, c_nx = 0, p_nx = 0;
+    double2 ob_cur = make_double2(0.0, 0.0), ob_nx = ob_cur;
+    const bool v0 = o < nobs, v1 = o + stride < nobs;
+    if (v0) { c_cur = cam_idx[o]; p_cur = pt_idx[o]; ob_cur = obs[o]; }
+    if (v1) { c_nx = cam_idx[o + stride]; p_nx = pt_idx[o + stride]; ob_nx = obs[o + stride]; }
     const double *ctab = camlin;
+    constexpr int CS = SMEM_CAMS ? K8_CAM_STRIDE : CAMLIN_STRIDE;
     if (SMEM_CAMS) {
-        for (int i = threadIdx.x; i < nc * CAMLIN_STRIDE; i += THREADS) scam[i] = camlin[i];
-        __syncthreads();
+        // 6 of the 11 16-byte words of every record
+        const double2 *src = reinterpret_cast<const double2 *>(camlin);
+        double2 *dst = reinterpret_cast<double2 *>(scam);
+        for (int i = threadIdx.x; i < nc * (K8_CAM_DOUBLES / 2); i += THREADS) {
+            const int c = i / (K8_CAM_DOUBLES / 2), j = i - c * (K8_CAM_DOUBLES / 2);
+            dst[c * (K8_CAM_STRIDE / 2) + j] = __ldg(src + c * (CAMLIN_STRIDE / 2) + j);
+        }
         ctab = scam;
     }
+    double X[3] = {0.0, 0.0, 0.0};
+    if (v0) { X[0] = pts[3 * (size_t)p_cur]; X[1] = pts[3 * (size_t)p_cur + 1]; X[2] = pts[3 * (size_t)p_cur + 2]; }
+    if (SMEM_CAMS) __syncthreads();
     double cost = 0.0;
-    const int stride = gridDim.x * THREADS;
-    // two observations in flight per thread: the pass is latency bound (16 warps per SM when the
-    // camera table fills shared memory), so the loads of both are issued before either is used
-    for (int o = blockIdx.x * THREADS + threadIdx.x; o < nobs; o += 2 * stride) {
-        const int o2 = o + stride;
-        const bool two = o2 < nobs;
-        const int c = cam_idx[o], p = pt_idx[o];
-        const int c2 = two ? cam_idx[o2] : c, p2 = two ? pt_idx[o2] : p;
-        const double2 ob = obs[o], ob2 = obs[two ? o2 : o];
-        double X[3] = {pts[3 * (size_t)p], pts[3 * (size_t)p + 1], pts[3 * (size_t)p + 2]};
-        double X2[3] = {pts[3 * (size_t)p2], pts[3 * (size_t)p2 + 1], pts[3 * (size_t)p2 + 2]};
-        CamLin cl, cl2;
-        const double *cp = ctab + (size_t)CAMLIN_STRIDE * c, *cp2 = ctab + (size_t)CAMLIN_STRIDE * c2;
-        camlin_load_proj(cp, cl);
-        camlin_load_proj(cp2, cl2);
-        double ru, rv, ru2, rv2;
-        ba_residual_only(cl, X, ob.x, ob.y, ru, rv);
-        ba_residual_only(cl2, X2, ob2.x, ob2.y, ru2, rv2);
+    for (; o < nobs; o += stride) {
+        const int o2 = o + 2 * stride;
+        int c_n2 = 0, p_n2 = 0;
+        double2 ob_n2 = make_double2(0.0, 0.0);
+        if (o2 < nobs) { c_n2 = cam_idx[o2]; p_n2 = pt_idx[o2]; ob_n2 = obs[o2]; }
+        double Xn[3] = {0.0, 0.0, 0.0};
+        if (o + stride < nobs) {
+            Xn[0] = pts[3 * (size_t)p_nx]; Xn[1] = pts[3 * (size_t)p_nx + 1]; Xn[2] = pts[3 * (size_t)p_nx + 2];
+        }
+        CamLin cl;
+        camlin_load_proj(ctab + (size_t)CS * c_cur, cl);
+        double ru, rv;
+        ba_residual_only(cl, X, ob_cur.x, ob_cur.y, ru, rv);
         cost += 0.5 * (ru * ru + rv * rv);
         if (r_out) r_out[o] = make_double2(ru, rv);
-        if (two) {
-            cost += 0.5 * (ru2 * ru2 + rv2 * rv2);
-            if (r_out) r_out[o2] = make_double2(ru2, rv2);
-        }
+        c_cur = c_nx; c_nx = c_n2; p_nx = p_n2;
+        ob_cur = ob_nx; ob_nx = ob_n2;
+        X[0] = Xn[0]; X[1] = Xn[1]; X[2] = Xn[2];
     }
     double s = block_sum(cost, sred);
     if (threadIdx.x == 0) costpart[blockIdx.x] = s;
@@ -1262,7 +1283,7 @@ static int launch_point_pass(const BAPlan &pl, const KParam &K, const double *ca
 
 static int launch_cost(const BAPlan &pl, const double *camlin, const double *pts, const double2 *obs,
                        const int32_t *cam_idx, const int32_t *pt_idx, double2 *r_out, cudaStream_t st) {
-    const size_t sm = pl.smem_cams ? pl.cam_smem : 0;
+    const size_t sm = pl.smem_cams ? (size_t)pl.nc * K8_CAM_STRIDE * sizeof(double) : 0;
 #define C_ARGS camlin, pl.nc, pts, obs, cam_idx, pt_idx, pl.nobs, pl.costpart, r_out
     if (pl.smem_cams) {
         if (pl.obs_threads >= 512) ba_cost_kernel<true, 768, 1><<<pl.grid_obs, 768, sm, st>>>(C_ARGS);
