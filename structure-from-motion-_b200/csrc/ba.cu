@@ -29,6 +29,7 @@
 // minimum (DESIGN.md "BA").
 #include "ba_math.cuh"
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <stdio.h>
 #include <string.h>
 #include <stdlib.h>
@@ -563,7 +564,7 @@ ba_schur_kernel(const double *__restrict__ W, int nobs, const int32_t *__restric
 __global__ void __launch_bounds__(256)
 ba_point_prep_kernel(const double *__restrict__ V, const double *__restrict__ gp, double *__restrict__ Dp, int npts,
                      double lambda, int update_D, int first, double *__restrict__ Vinv, double *__restrict__ bp,
-                     unsigned long long *__restrict__ gmax, int *__restrict__ fail) {
+                     unsigned long long *__restrict__ gmax, int *__restrict__ fail, double *__restrict__ Ginv = nullptr) {
     const int p = blockIdx.x * 256 + threadIdx.x;
     double gm = 0.0;
     if (p < npts) {
@@ -598,12 +599,250 @@ ba_point_prep_kernel(const double *__restrict__ V, const double *__restrict__ gp
         for (int i = 0; i < 6; ++i) Vinv[6 * (size_t)p + i] = vi[i];
 #pragma unroll
         for (int i = 0; i < 3; ++i) bp[3 * (size_t)p + i] = b[i];
+        if (Ginv) {
+            // G = C^-1 with (V + lambda Dp^2) = C C^T, so V^-1 = G^T G (K10g works with Z = W G^T).
+            // vi == 0 marks a failed factorisation: G = 0 gives the same zero contribution.
+            double gi[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+            if (vi[0] != 0.0 || vi[2] != 0.0 || vi[5] != 0.0) {
+                const double l00 = sqrt(v[0]), g00 = 1.0 / l00;
+                const double l10 = v[1] * g00, l20 = v[3] * g00;
+                const double l11 = sqrt(v[2] - l10 * l10), g11 = 1.0 / l11;
+                const double l21 = (v[4] - l20 * l10) * g11;
+                const double l22 = sqrt(v[5] - l20 * l20 - l21 * l21), g22 = 1.0 / l22;
+                gi[0] = g00;
+                gi[1] = -l10 * g00 * g11;
+                gi[2] = g11;
+                gi[4] = -l21 * g11 * g22;
+                gi[3] = -(l20 * g00 + l21 * gi[1]) * g22;
+                gi[5] = g22;
+            }
+#pragma unroll
+            for (int i = 0; i < 6; ++i) Ginv[6 * (size_t)p + i] = gi[i];
+            // h_p = G g_p: W_o b_p = W_o G^T G g_p = Z_o h_p, so the right-hand side comes out of the Z records too
+            double *H = Ginv + 6 * (size_t)npts;
+            H[3 * (size_t)p + 0] = gi[0] * g[0];
+            H[3 * (size_t)p + 1] = gi[1] * g[0] + gi[2] * g[1];
+            H[3 * (size_t)p + 2] = gi[3] * g[0] + gi[4] * g[1] + gi[5] * g[2];
+        }
     }
     if (update_D) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) gm = fmax(gm, __shfl_xor_sync(0xffffffffu, gm, o));
         if ((threadIdx.x & 31) == 0) atomic_max_pos(gmax, gm);
     }
+}
+
+// ---- K10g: the Schur complement as a GATHER over a plan-time pair list --------------------------
+// The point-major K10 sends 36 FP64 atomics to L2 for every camera pair of every point and runs
+// at the L2 atomic ceiling (~280 G adds/s on B200). Which observation pairs meet in which block
+// of S depends only on the index structure, so it is worked out once per problem:
+//   plan time : every pair (o_i, o_j) of observations of one point, keyed by its block
+//               (hi camera, lo camera), sorted by key with one CUB radix sort
+//   per trial : Z_o = W_o G_p^T per observation (G_p = inverse Cholesky factor of the damped V_p,
+//               so W_i V^-1 W_j^T = Z_i Z_j^T and ONE record type serves both sides), then a thread
+//               per slice of the sorted list accumulates Z_i Z_j^T in registers and sends 36 (21
+//               on the diagonal) atomics per (slice, block) instead of per (point, pair).
+constexpr int SG_THREADS = 128;
+
+__global__ void ba_pair_count_kernel(const int32_t *__restrict__ pt_ptr, const int32_t *__restrict__ cam_idx,
+                                     int npts, unsigned long long *__restrict__ count) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npts) return;
+    const int o0 = pt_ptr[p], k = pt_ptr[p + 1] - o0;
+    unsigned long long n = (unsigned long long)k * (k + 1) / 2;
+    for (int a = 1; a < k; ++a)                 // a camera named twice by one track: both orders are listed
+        for (int b = 0; b < a; ++b) n += (cam_idx[o0 + a] == cam_idx[o0 + b]) ? 1 : 0;
+    count[p] = n;
+}
+
+__global__ void ba_pair_emit_kernel(const int32_t *__restrict__ pt_ptr, const int32_t *__restrict__ cam_idx,
+                                    int npts, int nc, const unsigned long long *__restrict__ offset,
+                                    uint32_t *__restrict__ keys, uint2 *__restrict__ pairs) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npts) return;
+    const int o0 = pt_ptr[p], k = pt_ptr[p + 1] - o0;
+    size_t w = (size_t)offset[p];
+    for (int a = 0; a < k; ++a) {
+        const int ca = cam_idx[o0 + a];
+        for (int b = 0; b <= a; ++b) {
+            const int cb = cam_idx[o0 + b];
+            const int hi = ca >= cb ? ca : cb, lo = ca >= cb ? cb : ca;
+            // row observation = the one of the hi camera
+            const int oi = ca >= cb ? o0 + a : o0 + b, oj = ca >= cb ? o0 + b : o0 + a;
+            keys[w] = (uint32_t)hi * (uint32_t)nc + (uint32_t)lo;
+            pairs[w] = make_uint2((unsigned)oi, (unsigned)oj);
+            ++w;
+            if (a != b && ca == cb) {
+                keys[w] = (uint32_t)hi * (uint32_t)nc + (uint32_t)lo;
+                pairs[w] = make_uint2((unsigned)oj, (unsigned)oi);
+                ++w;
+            }
+        }
+    }
+}
+
+// Z [nobs,18] as an array of records (the gather reads whole records at random). Thread per
+// observation, W planes read coalesced; the 32 records of a warp are contiguous in Z, so they go
+// through shared memory and leave as 288 consecutive 16-byte words (whole sectors: scattered
+// half-sector stores made L2 fetch every line from DRAM before merging).
+__global__ void __launch_bounds__(256)
+ba_schur_z_kernel(const double *__restrict__ W, int nobs, const int32_t *__restrict__ pt_idx,
+                  const double *__restrict__ Ginv, double *__restrict__ Z) {
+    __shared__ __align__(16) double2 sz[8][288];
+    const int o = blockIdx.x * 256 + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (o < nobs) {
+        const int p = pt_idx[o];
+        double g[6];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) g[i] = Ginv[6 * (size_t)p + i];
+        double z[18];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+            const double w0 = W[(size_t)(3 * r) * nobs + o], w1 = W[(size_t)(3 * r + 1) * nobs + o],
+                         w2 = W[(size_t)(3 * r + 2) * nobs + o];
+            z[3 * r + 0] = w0 * g[0];
+            z[3 * r + 1] = w0 * g[1] + w1 * g[2];
+            z[3 * r + 2] = w0 * g[3] + w1 * g[4] + w2 * g[5];
+        }
+#pragma unroll
+        for (int i = 0; i < 9; ++i) sz[warp][9 * lane + i] = make_double2(z[2 * i], z[2 * i + 1]);
+    }
+    __syncwarp();
+    const int o_w = o - lane;                                   // first observation of this warp
+    if (o_w >= nobs) return;
+    const int words = 9 * min(32, nobs - o_w);
+    double2 *dst = reinterpret_cast<double2 *>(Z) + 9 * (size_t)o_w;
+    for (int c = lane; c < words; c += 32) dst[c] = sz[warp][c];
+}
+
+__device__ __forceinline__ void sg_flush(double *__restrict__ S, size_t ld, int nc, uint32_t key, double (&acc)[36],
+                                         double (&accg)[6], double *__restrict__ gred) {
+    const int hi = (int)(key / (uint32_t)nc), lo = (int)(key - (uint32_t)hi * (uint32_t)nc);
+    double *blk = S + (size_t)(6 * hi) * ld + 6 * lo;
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int q = 0; q < 6; ++q) {
+            if (hi != lo || q <= r) atomicAdd(blk + (size_t)r * ld + q, -acc[6 * r + q]);   // K11 reads the lower triangle only
+            acc[6 * r + q] = 0.0;
+        }
+    if (hi == lo) {
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+            atomicAdd(gred + 6 * hi + r, -accg[r]);
+            accg[r] = 0.0;
+        }
+    }
+}
+
+// Plan time: the sorted list re-laid for the gather. Slice t = entries [t seg, (t+1) seg) of the
+// sorted list; entry `it` of the 32 slices of warp w sits at ((w seg + it) 32 + lane), so a warp
+// reads its indices as one 128-byte and one 256-byte line per iteration. Padding entries carry
+// SG_DEAD as key and observation 0.
+constexpr uint32_t SG_DEAD = 0xFFFFFFFFu;
+__global__ void ba_pair_interleave_kernel(const uint32_t *__restrict__ keys, const uint2 *__restrict__ pairs,
+                                          size_t npairs, int seg, size_t npadded, uint32_t *__restrict__ keys_i,
+                                          uint2 *__restrict__ pairs_i) {
+    const size_t d = (size_t)blockIdx.x * blockDim.x + threadIdx.x;      // destination index
+    if (d >= npadded) return;
+    const size_t lane = d & 31, wi = d >> 5, w = wi / seg, it = wi - w * seg;
+    const size_t src = (w * 32 + lane) * (size_t)seg + it;
+    const bool ok = src < npairs;
+    keys_i[d] = ok ? keys[src] : SG_DEAD;
+    pairs_i[d] = ok ? pairs[src] : make_uint2(0u, 0u);
+}
+
+// Lane = one slice of `seg` consecutive entries of the sorted list. The two 144-byte records of
+// every lane's current entry are fetched by the WARP with cp.async (nine 16-byte words per record,
+// consecutive lanes on consecutive words, so a request covers whole records instead of 32
+// scattered sectors) straight into shared memory, one entry ahead of the arithmetic (two stages;
+// the indices run two entries ahead), and read back by their owner without bank conflicts
+// (record stride 9 x 16 B). The diagonal entries (o, o) -- one per observation, sorted by camera
+// -- also carry the reduced right-hand side g_red[c] -= Z_o h_p, which therefore needs no pass of
+// its own.
+constexpr size_t SG_SMEM = (size_t)(SG_THREADS / 32) * 2 * 2 * 32 * 9 * sizeof(double2);
+
+__device__ __forceinline__ void sg_fetch(double2 *__restrict__ dst, const double2 *__restrict__ Z2, uint2 me, int lane) {
+    // dst: [2][288] words of this warp and stage
+#pragma unroll
+    for (int rnd = 0; rnd < 9; ++rnd) {
+        const int c = lane + 32 * rnd, src = c / 9, part = c - 9 * src;
+        const unsigned oi = __shfl_sync(0xffffffffu, me.x, src), oj = __shfl_sync(0xffffffffu, me.y, src);
+        const unsigned s0 = (unsigned)__cvta_generic_to_shared(dst + c), s1 = (unsigned)__cvta_generic_to_shared(dst + 288 + c);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s0), "l"(Z2 + 9 * (size_t)oi + part));
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s1), "l"(Z2 + 9 * (size_t)oj + part));
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(SG_THREADS, 3)
+ba_schur_gather_kernel(const uint32_t *__restrict__ keys, const uint2 *__restrict__ pairs, int seg,
+                       const double *__restrict__ Z, const int32_t *__restrict__ pt_idx, const double *__restrict__ H,
+                       int nc, double *__restrict__ S, size_t ld, double *__restrict__ gred) {
+    extern __shared__ __align__(16) double2 srec[];      // [warp][stage][2][288]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t gw = (size_t)blockIdx.x * (SG_THREADS / 32) + warp;     // the grid covers the padded list exactly
+    const uint32_t *kp = keys + gw * (size_t)seg * 32 + lane;
+    const uint2 *pp = pairs + gw * (size_t)seg * 32 + lane;
+    double2 *wbuf = srec + (size_t)warp * (2 * 2 * 288);
+    double acc[36], accg[6];
+#pragma unroll
+    for (int i = 0; i < 36; ++i) acc[i] = 0.0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) accg[i] = 0.0;
+    const double2 *Z2 = reinterpret_cast<const double2 *>(Z);
+    uint32_t k_cur = kp[0], k_nx = seg > 1 ? kp[32] : SG_DEAD;
+    uint2 me_cur = pp[0], me_nx = seg > 1 ? pp[32] : make_uint2(0u, 0u);
+    uint32_t cur = k_cur;                                 // block being accumulated (SG_DEAD: nothing yet)
+    sg_fetch(wbuf, Z2, me_cur, lane);
+    for (int it = 0; it < seg; ++it) {
+        const uint32_t k = k_cur;
+        const uint2 me = me_cur;
+        k_cur = k_nx;
+        me_cur = me_nx;
+        if (it + 2 < seg) { k_nx = kp[(size_t)(it + 2) * 32]; me_nx = pp[(size_t)(it + 2) * 32]; }
+        if (it + 1 < seg) {
+            sg_fetch(wbuf + ((it + 1) & 1) * (2 * 288), Z2, me_cur, lane);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncwarp();
+        const double2 *ri = wbuf + (it & 1) * (2 * 288) + 9 * lane, *rj = ri + 288;
+        if (k != SG_DEAD) {
+            if (k != cur) {
+                sg_flush(S, ld, nc, cur, acc, accg, gred);
+                cur = k;
+            }
+            double b[18];
+#pragma unroll
+            for (int i = 0; i < 9; ++i) {
+                const double2 v = rj[i];
+                b[2 * i] = v.x;
+                b[2 * i + 1] = v.y;
+            }
+            double h[3] = {0.0, 0.0, 0.0};
+            if (me.x == me.y) {
+                const int p = pt_idx[me.x];
+                h[0] = H[3 * (size_t)p]; h[1] = H[3 * (size_t)p + 1]; h[2] = H[3 * (size_t)p + 2];
+            }
+#pragma unroll
+            for (int hh = 0; hh < 3; ++hh) {          // two rows of Z_i (three 16-byte words) at a time
+                const double2 a0 = ri[3 * hh], a1 = ri[3 * hh + 1], a2 = ri[3 * hh + 2];
+                const double ar[2][3] = {{a0.x, a0.y, a1.x}, {a1.y, a2.x, a2.y}};
+#pragma unroll
+                for (int rr = 0; rr < 2; ++rr) {
+#pragma unroll
+                    for (int q = 0; q < 6; ++q)
+                        acc[6 * (2 * hh + rr) + q] += ar[rr][0] * b[3 * q] + ar[rr][1] * b[3 * q + 1] + ar[rr][2] * b[3 * q + 2];
+                    accg[2 * hh + rr] += ar[rr][0] * h[0] + ar[rr][1] * h[1] + ar[rr][2] * h[2];   // h = 0 off the diagonal entries
+                }
+            }
+        }
+        __syncwarp();          // the stage is refilled two iterations from now: everyone is done reading it
+    }
+    if (cur != SG_DEAD) sg_flush(S, ld, nc, cur, acc, accg, gred);
 }
 
 // K10b: the Schur complement by block ROW. The L2's FP64 atomic adders top out near 280 G adds/s
@@ -1165,6 +1404,11 @@ struct BAPlan {
     // state
     double *cam[2], *pts[2], *camlin[2];
     double *W, *V, *gp, *Vinv, *bp, *tp, *U, *gc, *Upart, *Dc, *Dp, *S, *Spack, *Linv, *dc;
+    double *Z, *Ginv;                          // K10g: Z [nobs,18] records, G [np,6]
+    const uint32_t *pair_keys;                 // K10g pair list (device memory owned by the plan cache, not the workspace)
+    const uint2 *pair_vals;
+    size_t npairs;                             // padded length: (warps x seg x 32) entries, warp-interleaved
+    int pair_seg;
     double *costpart, *updpart, *scal, *red1;
     unsigned long long *gmax;
     int *flags;       // [0] index validation, [1] schur (vinv) failure, [2] cholesky failure
@@ -1234,6 +1478,9 @@ static size_t ba_layout(BAPlan &pl, unsigned char *base, int nc, int np, int nob
     CARVE(Vinv, double, D * 6 * np);
     CARVE(bp, double, D * 3 * np);
     CARVE(tp, double, D * 3 * np);
+    CARVE(Z, double, D * 18 * nobs);
+    CARVE(Ginv, double, D * 9 * np);       // G [np,6] followed by h = G g_p [np,3]
+    pl.pair_keys = nullptr; pl.pair_vals = nullptr; pl.npairs = 0; pl.pair_seg = 0;
     CARVE(U, double, D * (27 * nc + 8));   // [U 21nc | g_c 6nc | cost, ...]: ONE allreduce per linearisation
     pl.gc = pl.U + 21 * (size_t)nc;
     pl.red1 = pl.gc + 6 * (size_t)nc;
@@ -1359,6 +1606,94 @@ static int ba_build_index(BAPlan &pl, const double2 *obs, const int32_t *cam_idx
     return SFM_OK;
 }
 
+// K10g applies to problems large enough for the L2 atomic ceiling to matter; small ones (the wrapper's
+// bundle adjustments) keep the point-major K10 and skip the plan-time sort. Development switches:
+// SFM_SCHUR_PAIRS=0 turns it off, SFM_SCHUR_PAIRS_MIN=<observations> moves the threshold (default 16384).
+static bool schur_pairs_wanted(int nc, int nobs) {
+    const char *e = getenv("SFM_SCHUR_PAIRS");
+    if (e && e[0] == '0') return false;
+    if (schur_by_rows() || (getenv("SFM_SCHUR_SMEM") && getenv("SFM_SCHUR_SMEM")[0] == '1')) return false;
+    const char *m = getenv("SFM_SCHUR_PAIRS_MIN");
+    const int min_obs = m ? atoi(m) : 16384;
+    return nc <= 65535 && nobs >= min_obs;
+}
+
+// Plan time: the sorted (block key, observation pair) list of K10g. *keys == nullptr on return
+// means "not applicable" (switched off, too small, or more than 2^31 pairs).
+static int ba_build_pairs(const BAPlan &pl, const int32_t *cam_idx, cudaStream_t st, uint32_t **keys, uint2 **vals,
+                          size_t *npairs, int *seg_out) {
+    *keys = nullptr; *vals = nullptr; *npairs = 0; *seg_out = 0;
+    if (!schur_pairs_wanted(pl.nc, pl.nobs)) return SFM_OK;
+    const int np = pl.np;
+    unsigned long long *cnt = nullptr, *off = nullptr;
+    SFM_CUDA_TRY(cudaMallocAsync(&cnt, sizeof(unsigned long long) * ((size_t)np + 1), st));
+    SFM_CUDA_TRY(cudaMallocAsync(&off, sizeof(unsigned long long) * ((size_t)np + 1), st));
+    SFM_CUDA_TRY(cudaMemsetAsync(cnt + np, 0, sizeof(unsigned long long), st));
+    ba_pair_count_kernel<<<ceil_div(np, 256), 256, 0, st>>>(pl.pt_ptr, cam_idx, np, cnt);
+    SFM_LAUNCH_CHECK();
+    size_t tmp_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, cnt, off, np + 1, st);
+    void *tmp = nullptr;
+    SFM_CUDA_TRY(cudaMallocAsync(&tmp, tmp_bytes + 256, st));
+    SFM_CUDA_TRY(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, cnt, off, np + 1, st));
+    count_launch();
+    unsigned long long total = 0;
+    SFM_CUDA_TRY(cudaMemcpyAsync(&total, off + np, sizeof(total), cudaMemcpyDeviceToHost, st));
+    SFM_CUDA_TRY(cudaStreamSynchronize(st));
+    SFM_CUDA_TRY(cudaFreeAsync(tmp, st));
+    SFM_CUDA_TRY(cudaFreeAsync(cnt, st));
+    if (total == 0 || total > 0x7fffffffull) {
+        SFM_CUDA_TRY(cudaFreeAsync(off, st));
+        return SFM_OK;
+    }
+    const size_t P = (size_t)total;
+    uint32_t *k_in = nullptr, *k_out = nullptr;
+    unsigned long long *v_in = nullptr, *v_out = nullptr;
+    SFM_CUDA_TRY(cudaMallocAsync(&k_in, sizeof(uint32_t) * P, st));
+    SFM_CUDA_TRY(cudaMallocAsync(&v_in, sizeof(unsigned long long) * P, st));
+    SFM_CUDA_TRY(cudaMallocAsync(&k_out, sizeof(uint32_t) * P, st));
+    SFM_CUDA_TRY(cudaMallocAsync(&v_out, sizeof(unsigned long long) * P, st));
+    ba_pair_emit_kernel<<<ceil_div(np, 256), 256, 0, st>>>(pl.pt_ptr, cam_idx, np, pl.nc, off, k_in,
+                                                         reinterpret_cast<uint2 *>(v_in));
+    SFM_LAUNCH_CHECK();
+    int bits = 1;
+    while (bits < 32 && (1ull << bits) < (unsigned long long)pl.nc * (unsigned long long)pl.nc) ++bits;
+    size_t sort_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, k_in, k_out, v_in, v_out, (int)P, 0, bits, st);
+    SFM_CUDA_TRY(cudaMallocAsync(&tmp, sort_bytes + 256, st));
+    SFM_CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, sort_bytes, k_in, k_out, v_in, v_out, (int)P, 0, bits, st));
+    count_launch();
+    SFM_CUDA_TRY(cudaFreeAsync(tmp, st));
+    SFM_CUDA_TRY(cudaFreeAsync(k_in, st));
+    SFM_CUDA_TRY(cudaFreeAsync(v_in, st));
+    SFM_CUDA_TRY(cudaFreeAsync(off, st));
+    // slice length: long enough that the 36 atomics of a flush (which contend when few blocks take
+    // many entries, as at C3) are small next to the accumulation, short enough to leave a few hundred
+    // slices per SM. Measured on B200: C3 2384 / 2509 / 2588 LM iterations/s at 8 / 16 / 32, C5 flat
+    // (199-200) from 24 to 48, falling beyond 64 (development switch: SFM_SCHUR_SEG)
+    static int seg_forced = getenv("SFM_SCHUR_SEG") ? atoi(getenv("SFM_SCHUR_SEG")) : 0;
+    const size_t target = (size_t)sm_count() * 256;
+    int seg = (int)std::min<size_t>(48, std::max<size_t>(16, (P + target - 1) / target));
+    if (seg_forced > 0) seg = seg_forced;
+    const size_t nslices = (P + seg - 1) / seg;
+    const size_t nwarps = align_up((nslices + 31) / 32, SG_THREADS / 32);     // whole CTAs
+    const size_t npadded = nwarps * 32 * (size_t)seg;
+    uint32_t *k_i = nullptr;
+    unsigned long long *v_i = nullptr;
+    SFM_CUDA_TRY(cudaMallocAsync(&k_i, sizeof(uint32_t) * npadded, st));
+    SFM_CUDA_TRY(cudaMallocAsync(&v_i, sizeof(unsigned long long) * npadded, st));
+    ba_pair_interleave_kernel<<<(unsigned)((npadded + 255) / 256), 256, 0, st>>>(
+        k_out, reinterpret_cast<const uint2 *>(v_out), P, seg, npadded, k_i, reinterpret_cast<uint2 *>(v_i));
+    SFM_LAUNCH_CHECK();
+    SFM_CUDA_TRY(cudaFreeAsync(k_out, st));
+    SFM_CUDA_TRY(cudaFreeAsync(v_out, st));
+    *keys = k_i;
+    *vals = reinterpret_cast<uint2 *>(v_i);
+    *npairs = npadded;
+    *seg_out = seg;
+    return SFM_OK;
+}
+
 }  // namespace sfm
 
 using namespace sfm;
@@ -1383,6 +1718,10 @@ static bool g_attrs_set = false;
 struct PlanKey {
     const void *ws, *cam_idx;
     int nc, np, nobs, nchunks, max_track, has_dup;
+    uint32_t *pair_keys;      // K10g pair list of this problem (cudaMalloc'ed; freed when the entry is replaced or evicted)
+    uint2 *pair_vals;
+    size_t npairs;
+    int pair_seg;
 };
 static std::mutex g_plan_mu;
 static std::vector<PlanKey> g_plans;
@@ -1399,18 +1738,30 @@ static int ba_acquire_index(BAPlan &pl, bool reuse, const void *d_ws, const doub
                 pl.nchunks = pk.nchunks;
                 pl.max_track = pk.max_track;
                 pl.has_dup = pk.has_dup;
+                pl.pair_keys = pk.pair_keys; pl.pair_vals = pk.pair_vals; pl.npairs = pk.npairs; pl.pair_seg = pk.pair_seg;
                 return SFM_OK;
             }
     }
     int rc = ba_build_index(pl, obs, d_cam_idx, d_pt_idx, st);
     if (rc != SFM_OK) return rc;
+    uint32_t *pkeys = nullptr;
+    uint2 *pvals = nullptr;
+    size_t npairs = 0;
+    int pseg = 0;
+    if ((rc = ba_build_pairs(pl, d_cam_idx, st, &pkeys, &pvals, &npairs, &pseg)) != SFM_OK) return rc;
+    pl.pair_keys = pkeys; pl.pair_vals = pvals; pl.npairs = npairs; pl.pair_seg = pseg;
     std::lock_guard<std::mutex> g(g_plan_mu);
-    PlanKey pk{d_ws, d_cam_idx, n_cams, n_pts, n_obs, pl.nchunks, pl.max_track, pl.has_dup};
+    PlanKey pk{d_ws, d_cam_idx, n_cams, n_pts, n_obs, pl.nchunks, pl.max_track, pl.has_dup, pkeys, pvals, npairs, pseg};
+    auto release = [st](PlanKey &q) {           // stream-ordered: kernels already queued on st still see the arrays
+        if (q.pair_keys) cudaFreeAsync(q.pair_keys, st);
+        if (q.pair_vals) cudaFreeAsync(q.pair_vals, st);
+        q.pair_keys = nullptr; q.pair_vals = nullptr; q.npairs = 0;
+    };
     bool found = false;
     for (PlanKey &q : g_plans)
-        if (q.ws == d_ws) { q = pk; found = true; }
+        if (q.ws == d_ws) { release(q); q = pk; found = true; }
     if (!found) {
-        if (g_plans.size() >= 16) g_plans.erase(g_plans.begin());
+        if (g_plans.size() >= 16) { release(g_plans.front()); g_plans.erase(g_plans.begin()); }
         g_plans.push_back(pk);
     }
     return SFM_OK;
@@ -1539,7 +1890,24 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
             SFM_LAUNCH_CHECK();
         }
         SchurRanges rg;
-        if (!schur_by_rows() && schur_smem_ranges(nc, pl.max_track, rg)) {
+        if (pl.npairs) {
+            // K10g: prep (V^-1, b_p, G), Z records + right-hand side, gather over the sorted pair list
+            ba_point_prep_kernel<<<ceil_div(np, 256), 256, 0, st>>>(pl.V, pl.gp, pl.Dp, np, lambda, update_D, first_lin,
+                                                                   pl.Vinv, pl.bp, pl.gmax, pl.flags + 1, pl.Ginv);
+            SFM_LAUNCH_CHECK();
+            ba_schur_z_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(pl.W, nobs, d_pt_idx, pl.Ginv, pl.Z);
+            SFM_LAUNCH_CHECK();
+            static bool sg_attr = false;
+            if (!sg_attr) {
+                cudaFuncSetAttribute(ba_schur_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SG_SMEM);
+                sg_attr = true;
+            }
+            const size_t nwarps = pl.npairs / ((size_t)pl.pair_seg * 32);
+            ba_schur_gather_kernel<<<(unsigned)(nwarps / (SG_THREADS / 32)), SG_THREADS, SG_SMEM, st>>>(
+                pl.pair_keys, pl.pair_vals, pl.pair_seg, pl.Z, d_pt_idx, pl.Ginv + 6 * (size_t)np, nc, pl.S, pl.ld,
+                pl.S + (size_t)pl.npad * pl.ld);
+            SFM_LAUNCH_CHECK();
+        } else if (!schur_by_rows() && schur_smem_ranges(nc, pl.max_track, rg)) {
             ba_point_prep_kernel<<<ceil_div(np, 256), 256, 0, st>>>(pl.V, pl.gp, pl.Dp, np, lambda, update_D, first_lin,
                                                                    pl.Vinv, pl.bp, pl.gmax, pl.flags + 1);
             SFM_LAUNCH_CHECK();
