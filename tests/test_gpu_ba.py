@@ -16,6 +16,18 @@ COST_RTOL = 1e-6
 RMSE_ATOL = 1e-3
 
 
+@pytest.fixture(params=["k10_atomic", "k10g_pairs"])
+def schur_path(request, monkeypatch):
+    """Both Schur-complement kernels on the same small problems: the L2-atomic K10 (default below 16384
+    observations) and the plan-time pair-list gather K10g (default above), forced through the library's
+    development switches, which are read at every index build."""
+    if request.param == "k10g_pairs":
+        monkeypatch.setenv("SFM_SCHUR_PAIRS_MIN", "0")
+    else:
+        monkeypatch.setenv("SFM_SCHUR_PAIRS", "0")
+    return request.param
+
+
 def _x0(sc):
     from scipy.spatial.transform import Rotation
     cams = np.array([np.hstack([Rotation.from_matrix(R).as_rotvec(), -R @ C]) for R, C in zip(sc["R0"], sc["C0"])])
@@ -74,7 +86,7 @@ def test_ba_residuals_match_reference(cuda_device, tag):
 
 
 @pytest.mark.parametrize("tag", ["a", "b"])
-def test_perform_bundle_adjustment_matches_reference(cuda_device, tag):
+def test_perform_bundle_adjustment_matches_reference(cuda_device, schur_path, tag):
     from sfm_b200 import bundle
     g = golden(f"ba_{tag}.npz")
     nc, npts, nobs = len(g["R0"]), len(g["pts0"]), len(g["cam_idx"])
@@ -106,7 +118,7 @@ def test_perform_bundle_adjustment_matches_reference(cuda_device, tag):
 
 
 @pytest.mark.parametrize("nc,npts,k,seed", [(8, 150, 5, 7), (12, 300, 6, 9), (20, 800, 7, 11)])
-def test_ba_sparse_matches_oracle_lm(cuda_device, nc, npts, k, seed):
+def test_ba_sparse_matches_oracle_lm(cuda_device, schur_path, nc, npts, k, seed):
     from sfm_b200 import bundle, scenes
     sc = scenes.ba_scene(n_cams=nc, n_pts=npts, obs_per_pt=k, seed=seed)
     cams0, pts0 = _x0(sc)
@@ -122,7 +134,7 @@ def test_ba_sparse_matches_oracle_lm(cuda_device, nc, npts, k, seed):
     assert info["status"] in (1, 2, 3, 4) and info["n_linearisations"] <= 30
 
 
-def test_ba_long_tracks_and_duplicate_cameras(cuda_device):
+def test_ba_long_tracks_and_duplicate_cameras(cuda_device, schur_path):
     """Points seen by more than 32 cameras take the global-memory Schur path; an observation list
     that names the same camera twice on one point must still match the oracle."""
     from sfm_b200 import bundle, scenes
@@ -213,3 +225,31 @@ def test_ba_c3_scale_properties(cuda_device):
     # bit-reproducible
     cams2, pts2, info2 = bundle.ba_solve_sparse(cams0, pts0, sc["cam_idx"], sc["pt_idx"], sc["obs"], sc["K"])
     assert info2["cost"] == info["cost"] or abs(info2["cost"] - info["cost"]) / info["cost"] < 1e-12
+
+
+def test_schur_pair_list_equals_atomic_path(cuda_device, monkeypatch):
+    """K10g against K10 on one damped trial system: same parameters after a fixed number of trial steps
+    (the two kernels sum the same products in different orders, so agreement is to rounding, far inside
+    the 1e-6 cost tolerance), on a scene with long tracks, duplicated cameras and a camera seen once."""
+    from sfm_b200 import bundle, scenes
+    sc = scenes.ba_scene(n_cams=30, n_pts=2500, obs_per_pt=9, seed=5)
+    cam_idx, pt_idx, obs = sc["cam_idx"].copy(), sc["pt_idx"].copy(), sc["obs"].copy()
+    dup = np.arange(3, len(cam_idx), 101)
+    c2 = np.concatenate([cam_idx, cam_idx[dup]])
+    p2 = np.concatenate([pt_idx, pt_idx[dup]])
+    o2 = np.concatenate([obs, obs[dup] + 0.2])
+    order = np.argsort(p2, kind="stable")
+    c2, p2, o2 = c2[order], p2[order], o2[order]
+    cams0, pts0 = _x0(sc)
+    out = {}
+    for name, env in (("atomic", {"SFM_SCHUR_PAIRS": "0"}), ("pairs", {"SFM_SCHUR_PAIRS_MIN": "0"})):
+        monkeypatch.delenv("SFM_SCHUR_PAIRS", raising=False)
+        monkeypatch.delenv("SFM_SCHUR_PAIRS_MIN", raising=False)
+        for k_, v_ in env.items():
+            monkeypatch.setenv(k_, v_)
+        cams, pts, info = bundle.ba_solve_sparse(cams0, pts0, c2, p2, o2, sc["K"])
+        out[name] = (cams, pts, info)
+    (ca, pa, ia), (cb, pb, ib) = out["atomic"], out["pairs"]
+    assert ia["n_trials"] == ib["n_trials"] and ia["status"] == ib["status"]
+    assert abs(ia["cost"] - ib["cost"]) / ia["cost"] < 1e-10
+    assert rel_err(cb, ca) < 1e-7 and rel_err(pb, pa) < 1e-7
