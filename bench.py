@@ -328,7 +328,7 @@ def run_ours(args, rank, world):
             out["gpu_launches"] += ba_mgpu["gpu_launches"]
         clocks.__exit__()
         out["clocks"] = clocks.summary()
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -348,6 +348,12 @@ def main():
     # some launch environments) would otherwise land in front of it
     if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
         os.environ["NCCL_DEBUG"] = "WARN"
+    # ... and anything else a library writes to file descriptor 1 goes to stderr; print() below still reaches
+    # the real stdout through the saved descriptor
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:
