@@ -323,6 +323,10 @@ def run_ours(args, rank, world):
                 before = _lib.launch_count()
                 out["c1_pipeline"] = bench_pipeline.run()
                 out["c1_pipeline"]["gpu_launches"] = int(_lib.launch_count() - before)
+                import bench_c4
+                before = _lib.launch_count()
+                out["c4_batched_solvers"] = bench_c4.run(flush)
+                out["c4_batched_solvers"]["gpu_launches"] = int(_lib.launch_count() - before)
         if ba_mgpu is not None:
             out["ba"] = ba_mgpu
             out["gpu_launches"] += ba_mgpu["gpu_launches"]
