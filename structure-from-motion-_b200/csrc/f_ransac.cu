@@ -441,6 +441,24 @@ static int pick_chunk(int n, int h) {
     return chunk;
 }
 
+// The same for the filter kernels, which run exactly `per_sm` CTAs per SM: all CTAs do the same
+// work, so the grid should fill whole waves. Picks the smallest number of waves w for which
+// floor(w * slots / tiles) point chunks of at most 1024 (even) correspondences cover n. Matters for
+// the drop-in's chunked launches (2k-25k hypotheses each): a 2,048-hypothesis launch was 1.32
+// waves with the power-of-two rule above.
+static int pick_chunk_waves(int n, int h, int per_sm) {
+    const long long tiles = ceil_div(h, K2_THREADS), slots = (long long)per_sm * sm_count();
+    for (long long w = 1; w <= 4096; ++w) {
+        const long long nchunks = w * slots / tiles;
+        if (nchunks < 1) continue;
+        long long chunk = (n + nchunks - 1) / nchunks;
+        chunk += chunk & 1;                    // even: the packed kernel works on pairs
+        if (chunk < 128) chunk = 128;
+        if (chunk <= 1024) return (int)chunk;
+    }
+    return 1024;
+}
+
 }  // namespace sfm
 
 using namespace sfm;
@@ -461,7 +479,7 @@ static int f_score_launch(const double *d_x1x2, int32_t n, const double *d_F, in
     cudaStream_t st = as_stream(stream);
     SFM_CUDA_TRY(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)h, st));
     if (n == 0) return SFM_OK;
-    int chunk = pick_chunk(n, h);
+    int chunk = all_fp64 ? pick_chunk(n, h) : pick_chunk_waves(n, h, 4);
     dim3 grid(ceil_div(h, K2_THREADS), ceil_div(n, chunk));
     if (!all_fp64) {
         // development switch: the scalar-FP32 filter the packed kernel replaced
