@@ -94,8 +94,29 @@ def run(flush=None, with_cpu=True):
            "algorithmic_gbs": {"lintri (56 B/point)": 56.0 * N_PTS / (ms_lin * 1e-3) / 1e9,
                                "nltri (80 B/point)": 80.0 * N_PTS / (ms_nl * 1e-3) / 1e9},
            "bound": "FP64 latency / issue (thread per point, register-resident LM); not an HBM stream"}
+    # PnPRANSAC (reference defaults threshold=200, n_max=1000) through the drop-in, host arrays in/out: the
+    # 4-point LinearPnP hypotheses stay on host LAPACK, scoring + first-maximum on the GPU
+    import random
+    from sfm_b200 import pnp_ransac
+    n_rr = 40
+    random.seed(777)
+    pnp_ransac.PnPRANSAC(Xs[0], xs[0], scenes.K_REF)                      # warm
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for b in range(n_rr):
+        pnp_ransac.PnPRANSAC(Xs[b], xs[b], scenes.K_REF)
+    torch.cuda.synchronize()
+    out["pnp_ransac_registrations_s"] = n_rr / (time.perf_counter() - t0)
+    out["pnp_ransac_note"] = (f"{n_rr} registrations of {N_CORR} correspondences x 1000 hypotheses, end to end from host "
+                              "arrays; hypotheses by batched host LAPACK, scoring and argmax on the GPU")
     if with_cpu:
         out["cpu_baseline"] = cpu_baseline(sc)
+        from oracle import sfm_oracle as so
+        random.seed(777)
+        t0 = time.perf_counter()
+        for b in range(4):
+            so.pnp_ransac(Xs[b], xs[b], scenes.K_REF, 200, 1000)
+        out["cpu_baseline"]["pnp_ransac_registrations_s"] = 4 / (time.perf_counter() - t0)
     return out
 
 
