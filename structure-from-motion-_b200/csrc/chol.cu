@@ -403,12 +403,13 @@ __device__ __forceinline__ void dmma_884(double &d0, double &d1, double a, doubl
                  : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
-// Tile t of a phase-2 step belongs to: tile 0 (holds the next diagonal block) -> CTA 0, which then
-// factors that block; every other tile round-robin over CTAs 1 .. G-1.
-__device__ __forceinline__ int st_first_tile(int cta, int G) { return (G == 1 || cta == 0) ? 0 : cta; }
+// Phase-2 work split (G > 1): CTA 0 is the critical path -- it updates ONLY the next diagonal block
+// (one 48 x 48 product with the block it solved in phase 1) and factors it right away; the
+// super-tiles, with that block masked out of tile 0, go round-robin over CTAs 1 .. G-1. (CTA 0 used
+// to take the whole 96 x 96 tile 0 before factoring: ~4 us more on the chain of every panel.)
+__device__ __forceinline__ int st_first_tile(int cta, int G) { return G == 1 ? 0 : (cta == 0 ? 0x3fffffff : cta - 1); }
 __device__ __forceinline__ int st_next_tile(int t, int cta, int G) {
     if (G == 1) return t + 1;
-    if (cta == 0) return 0x3fffffff;
     return t + (G - 1);
 }
 
@@ -416,9 +417,23 @@ template <bool DMMA, class FactorFn>
 __device__ void supertile_phase(CholSmem &sm, double *A, size_t ld, const unsigned char *nz, int k, int nb,
                                 int cta, int G, FactorFn &factor_next) {
     double *buf = sm.buf;
+    const int kcol = k * CH_NB, lo = (k + 1) * CH_NB, row_lim = (nb + 1) * CH_NB, col_lim = nb * CH_NB;
+    const bool split = G > 1;
+    if (split && cta == 0) {
+        double *const sL = buf, *const sC = buf + 2 * CH_NB * CH_LDS;
+        __syncthreads();                          // the phase-1 views of buf are dead from here on
+        load_block(sL, A, ld, lo, kcol);
+        load_block(sC, A, ld, lo, lo);
+        __syncthreads();
+        block_xyT<1>(sL, sL, sC);                 // A_{k+1,k+1} -= L_{k+1,k} L_{k+1,k}^T
+        __syncthreads();
+        store_block(sC, A, ld, lo, lo);
+        factor_next(k + 1);
+        return;
+    }
+    const int dlim = split ? lo + CH_NB : lo;     // rows and columns both below dlim: CTA 0's block
     SuperTiles st;
     st.init(sm, nz, k, nb);
-    const int kcol = k * CH_NB, lo = (k + 1) * CH_NB, row_lim = (nb + 1) * CH_NB, col_lim = nb * CH_NB;
     int t = st_first_tile(cta, G), I = 0, J = 0, stage = 0;
     __syncthreads();                              // the phase-1 views of buf are dead from here on
     if (t < st.ntiles) {
@@ -451,7 +466,7 @@ __device__ void supertile_phase(CholSmem &sm, double *A, size_t ld, const unsign
 #pragma unroll
                 for (int b = 0; b < 3; ++b) {
                     const int c = c0 + 8 * b;       // c even, col_lim and lo even: the pair is in or out together
-                    if (r < row_lim && r >= lo && c < col_lim && c >= lo) {
+                    if (r < row_lim && r >= lo && c < col_lim && c >= lo && !(r < dlim && c < dlim)) {
                         const double2 v = *reinterpret_cast<const double2 *>(&A[(size_t)r * ld + c]);
                         acc[a][b][0] = v.x; acc[a][b][1] = v.y;
                     } else {
@@ -482,7 +497,7 @@ __device__ void supertile_phase(CholSmem &sm, double *A, size_t ld, const unsign
 #pragma unroll
                 for (int b = 0; b < 3; ++b) {
                     const int c = c0 + 8 * b;
-                    if (c < col_lim && c >= lo)
+                    if (c < col_lim && c >= lo && !(r < dlim && c < dlim))
                         *reinterpret_cast<double2 *>(&A[(size_t)r * ld + c]) = make_double2(acc[a][b][0], acc[a][b][1]);
                 }
             }
@@ -495,7 +510,7 @@ __device__ void supertile_phase(CholSmem &sm, double *A, size_t ld, const unsign
 #pragma unroll
                 for (int b = 0; b < 6; ++b) {
                     const int c = J * CH_ST + tx + 16 * b;
-                    acc[a][b] = (r < row_lim && r >= lo && c < col_lim && c >= lo) ? A[(size_t)r * ld + c] : 0.0;
+                    acc[a][b] = (r < row_lim && r >= lo && c < col_lim && c >= lo && !(r < dlim && c < dlim)) ? A[(size_t)r * ld + c] : 0.0;
                 }
             }
             cp_async_wait<1>();
@@ -522,12 +537,12 @@ __device__ void supertile_phase(CholSmem &sm, double *A, size_t ld, const unsign
 #pragma unroll
                 for (int b = 0; b < 6; ++b) {
                     const int c = J * CH_ST + tx + 16 * b;
-                    if (c < col_lim && c >= lo) A[(size_t)r * ld + c] = acc[a][b];
+                    if (c < col_lim && c >= lo && !(r < dlim && c < dlim)) A[(size_t)r * ld + c] = acc[a][b];
                 }
             }
         }
         __syncthreads();                          // this stage may be refilled by the next iteration's loads
-        if (t == 0) factor_next(k + 1);           // look-ahead: tile 0 holds the next diagonal block; its
+        if (t == 0 && !split) factor_next(k + 1); // single CTA: tile 0 holds the next diagonal block; its
                                                   // factor works in this (now free) stage's first 3 views
         stage ^= 1;
         t = tn;
