@@ -605,26 +605,47 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
         // ---- phase 1: panel solve A_ik <- A_ik L_kk^-T with the inverse committed one phase earlier ----
         const int rows_below = nb - k;            // block-rows k+1 .. nb (nb = RHS)
         if (cta < rows_below) {
-            for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
-                int r = e / CH_NB, c = e - r * CH_NB;
-                sB[r * CH_LDS + c] = Linv_ws[(size_t)k * CH_NB * CH_NB + e];
+            // the inverse and the first block of this CTA are requested together (18 independent loads per
+            // thread, one L2 round trip) before anything is parked in shared memory
+            constexpr int PER = CH_NB * CH_NB / CH_THREADS;       // 9
+            double lv[PER], bv[PER];
+            int i = k + 1 + cta;
+#pragma unroll
+            for (int u = 0; u < PER; ++u) lv[u] = Linv_ws[(size_t)k * CH_NB * CH_NB + threadIdx.x + u * CH_THREADS];
+#pragma unroll
+            for (int u = 0; u < PER; ++u) {
+                const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                bv[u] = A[(size_t)(i * CH_NB + r) * ld + k * CH_NB + c];
             }
-            for (int i = k + 1 + cta; i <= nb; i += G) {
-                __syncthreads();
+#pragma unroll
+            for (int u = 0; u < PER; ++u) {
+                const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                sB[r * CH_LDS + c] = lv[u];
+            }
+            for (; i <= nb; i += G) {
                 int any = 0;
-                for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
-                    int r = e / CH_NB, c = e - r * CH_NB;
-                    const double v = A[(size_t)(i * CH_NB + r) * ld + k * CH_NB + c];
-                    sC[r * CH_LDS + c] = v;
-                    any |= !(v == 0.0);
+#pragma unroll
+                for (int u = 0; u < PER; ++u) {
+                    const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                    sC[r * CH_LDS + c] = bv[u];
+                    any |= !(bv[u] == 0.0);
+                }
+                if (i + G <= nb) {                // next block of this CTA (only when rows outnumber CTAs)
+#pragma unroll
+                    for (int u = 0; u < PER; ++u) {
+                        const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                        bv[u] = A[(size_t)((i + G) * CH_NB + r) * ld + k * CH_NB + c];
+                    }
                 }
                 any = __syncthreads_or(any);
                 if (threadIdx.x == 0) nz[(size_t)i * nb + k] = (unsigned char)(any != 0);
-                if (!any) continue;               // an exactly zero block stays zero
-                // X = A_ik L^-T : X[r][c] = sum_m A_ik[r][m] Linv[c][m]
-                block_xyT<0>(sC, sB, sL);
-                __syncthreads();
-                store_block(sL, A, ld, i * CH_NB, k * CH_NB);
+                if (any) {                        // an exactly zero block stays zero
+                    // X = A_ik L^-T : X[r][c] = sum_m A_ik[r][m] Linv[c][m]
+                    block_xyT<0>(sC, sB, sL);
+                    __syncthreads();
+                    store_block(sL, A, ld, i * CH_NB, k * CH_NB);
+                }
+                __syncthreads();                  // sC / sL are rewritten by the next block
             }
         }
         CH_TICK(1);
@@ -711,6 +732,9 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
         CH_TICK(5);
         return;
     }
+    // (A single-CTA left-looking substitution for block-sparse factors was tried here: one SM cannot pull
+    // the ~10 non-zero blocks of a block column from L2 fast enough -- 5.7 us per step against 4.3 us for
+    // the grid-wide steps below at C5 -- so the grid-wide form serves sparse and dense factors alike.)
     for (int e = cta * CH_THREADS + threadIdx.x; e < nb * CH_NB; e += G * CH_THREADS) x_out[e] = yrow[e];
     grid.sync();
     for (int k = nb - 1; k >= 0; --k) {
