@@ -552,6 +552,62 @@ __device__ void supertile_phase(CholSmem &sm, double *A, size_t ld, const unsign
     cp_async_wait<0>();
 }
 
+// ---- phase 2 for block-sparse panels (CTAs 1 .. G-1 of a split grid) ----
+// When only a few block-rows below the diagonal hold a non-zero panel block (banded / arrowhead reduced
+// camera systems: ~10 of 125 at C5), 96 x 96 super-tiles mostly multiply zeros and their ~13 us per tile
+// outlast CTA 0's syrk + factor chain (10 us). Here the active block-rows are listed at 48-block
+// granularity and the tiles (I, J), I >= J both active, are plain 48 x 48 products, one or two per CTA.
+// Returns false (nothing done) when more than CH_SPARSE_ROWS rows are active: the caller then runs the
+// super-tile phase. Every CTA reaches the same verdict from the same flags. Measured at C5 (a trailing
+// CTA's phase 2): 3.6 us per panel; the panel step is then bounded by CTA 0's chain alone (syrk + 48 x 48
+// factor + commit, 10.5 us) plus the two grid barriers.
+constexpr int CH_SPARSE_ROWS = 24;
+
+__device__ bool sparse_tile_phase(CholSmem &sm, double *A, size_t ld, const unsigned char *nz, int k, int nb,
+                                  int cta, int G) {
+    double *const sL = sm.buf, *const sB = sm.buf + CH_NB * CH_LDS, *const sC = sm.buf + 2 * CH_NB * CH_LDS;
+    __syncthreads();                              // the phase-1 views of buf and sm.act are free from here on
+    if (threadIdx.x < 32) {
+        int base = 0;
+        for (int i0 = k + 1; i0 < nb && base <= CH_SPARSE_ROWS; i0 += 32) {
+            const int i = i0 + (int)threadIdx.x;
+            const bool a = i < nb && nz[(size_t)i * nb + k];
+            const unsigned m = __ballot_sync(0xffffffffu, a);
+            const int at = base + __popc(m & ((1u << threadIdx.x) - 1u));
+            if (a && at <= CH_SPARSE_ROWS) sm.act[at] = (short)i;
+            base += __popc(m);
+        }
+        if (threadIdx.x == 0) sm.nact = base;     // block columns; the right-hand-side row is implicit
+    }
+    __syncthreads();
+    const int nJ = sm.nact;
+    if (nJ > CH_SPARSE_ROWS) return false;
+    const int tri = nJ * (nJ + 1) / 2, ntiles = tri + nJ, lo = k + 1;
+    for (int t = cta - 1; t < ntiles; t += G - 1) {
+        int Ip, Jp;
+        if (t < tri) {
+            Ip = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
+            while ((Ip + 1) * (Ip + 2) / 2 <= t) ++Ip;
+            while (Ip * (Ip + 1) / 2 > t) --Ip;
+            Jp = t - Ip * (Ip + 1) / 2;
+        } else {
+            Ip = nJ;
+            Jp = t - tri;
+        }
+        const int I = Ip < nJ ? sm.act[Ip] : nb, J = sm.act[Jp];
+        if (I == lo && J == lo) continue;         // the next diagonal block: CTA 0 updates and factors it
+        __syncthreads();
+        load_block(sL, A, ld, I * CH_NB, k * CH_NB);
+        load_block(sB, A, ld, J * CH_NB, k * CH_NB);
+        load_block(sC, A, ld, I * CH_NB, J * CH_NB);
+        __syncthreads();
+        block_xyT<1>(sL, sB, sC);
+        __syncthreads();
+        store_block(sC, A, ld, I * CH_NB, J * CH_NB);
+    }
+    return true;
+}
+
 // nb = npad / NB diagonal blocks; block-row nb is the right-hand side. x_out [npad].
 // Linv_ws [nb, NB*NB]: inverses of the diagonal factors (for the backward substitution).
 template <bool DMMA>
@@ -657,7 +713,8 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
         const int m = nb - 1 - k;                 // remaining diagonal blocks
         if (m >= CH_SUPER_MIN) {
             // 96 x 96 super-tiles over the trailing block rows k+1 .. nb, aligned to even block indices
-            supertile_phase<DMMA>(sm, A, ld, nz, k, nb, cta, G, factor_and_commit);
+            if (G == 1 || cta == 0 || !sparse_tile_phase(sm, A, ld, nz, k, nb, cta, G))
+                supertile_phase<DMMA>(sm, A, ld, nz, k, nb, cta, G, factor_and_commit);
         } else if (m > 0) {
             // tiles: for j' in [0, m): i' in [j', m]  (i' == m is the RHS block-row)
             const int ntiles = m * (m + 1) / 2 + m;
