@@ -641,9 +641,12 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
     } while (0)
 
     // Diagonal block kb: factor it, commit L_kb,kb to A and its inverse to Linv_ws (CTA 0 only).
-    auto factor_and_commit = [&](int kb) {
+    // src != nullptr: the (already updated) block sits in shared memory (row stride CH_LDS, beyond the four
+    // views the factor uses) instead of in A.
+    auto factor_and_commit = [&](int kb, const double *src = nullptr) {
         __syncthreads();
-        factor_diag_block(sm, A + (size_t)kb * CH_NB * ld + kb * CH_NB, ld, prof);
+        if (src) factor_diag_block(sm, src, (size_t)CH_LDS, prof);
+        else factor_diag_block(sm, A + (size_t)kb * CH_NB * ld + kb * CH_NB, ld, prof);
         store_block(sL, A, ld, kb * CH_NB, kb * CH_NB);
         for (int e = threadIdx.x; e < CH_NB * CH_NB; e += CH_THREADS) {
             int r = e / CH_NB, c = e - r * CH_NB;
@@ -657,98 +660,242 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
     grid.sync();
     CH_TICK(2);
 
-    for (int k = 0; k < nb; ++k) {
-        // ---- phase 1: panel solve A_ik <- A_ik L_kk^-T with the inverse committed one phase earlier ----
-        const int rows_below = nb - k;            // block-rows k+1 .. nb (nb = RHS)
-        if (cta < rows_below) {
-            // the inverse and the first block of this CTA are requested together (18 independent loads per
-            // thread, one L2 round trip) before anything is parked in shared memory
-            constexpr int PER = CH_NB * CH_NB / CH_THREADS;       // 9
-            double lv[PER], bv[PER];
-            int i = k + 1 + cta;
-#pragma unroll
-            for (int u = 0; u < PER; ++u) lv[u] = Linv_ws[(size_t)k * CH_NB * CH_NB + threadIdx.x + u * CH_THREADS];
-#pragma unroll
-            for (int u = 0; u < PER; ++u) {
-                const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
-                bv[u] = A[(size_t)(i * CH_NB + r) * ld + k * CH_NB + c];
-            }
-#pragma unroll
-            for (int u = 0; u < PER; ++u) {
-                const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
-                sB[r * CH_LDS + c] = lv[u];
-            }
-            for (; i <= nb; i += G) {
-                int any = 0;
-#pragma unroll
-                for (int u = 0; u < PER; ++u) {
-                    const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
-                    sC[r * CH_LDS + c] = bv[u];
-                    any |= !(bv[u] == 0.0);
-                }
-                if (i + G <= nb) {                // next block of this CTA (only when rows outnumber CTAs)
+    const bool split = G > 1;
+    if (split) {
+        // ---- critical-path form (G > 1) ----
+        // The dependency chain of a blocked Cholesky is trsm(k+1,k) -> syrk(k+1,k+1) -> factor(k+1), once
+        // per panel. CTA 0 runs exactly that chain and nothing else, without waiting for anybody inside a
+        // panel step: L_kk^-1 is still in its shared memory from the factor it just finished, it solves
+        // block (k+1,k), publishes it (`ready` = k+1, release), updates and factors the next diagonal block.
+        // CTAs 1 .. G-1 solve the other block-rows of the panel, meet at a barrier of their own, wait for
+        // `ready` (set long before) and run the trailing update. One grid-wide barrier per panel remains.
+        unsigned *const syncw = reinterpret_cast<unsigned *>(nz + (((size_t)(nb + 1) * nb + 15) & ~(size_t)15));
+        unsigned *const bar_ctr = syncw, *const ready = syncw + 1;      // zeroed by chol_solve_launch
+        const unsigned P = (unsigned)(G - 1);
+        for (int k = 0; k < nb; ++k) {
+            if (cta == 0) {
+                if (k + 1 < nb) {
+                    const int i = k + 1;
+                    constexpr int PER = CH_NB * CH_NB / CH_THREADS;       // 9
+                    double *const sD = sm.buf + 4 * CH_NB * CH_LDS;       // fifth view: outside the factor's four
+                    // both blocks the chain needs are final since the last grid barrier: one L2 round trip
+                    double bv[PER], dv[PER];
 #pragma unroll
                     for (int u = 0; u < PER; ++u) {
                         const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
-                        bv[u] = A[(size_t)((i + G) * CH_NB + r) * ld + k * CH_NB + c];
+                        bv[u] = A[(size_t)(i * CH_NB + r) * ld + k * CH_NB + c];
+                        dv[u] = A[(size_t)(i * CH_NB + r) * ld + i * CH_NB + c];
+                    }
+                    int any = 0;
+#pragma unroll
+                    for (int u = 0; u < PER; ++u) {
+                        const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                        sC[r * CH_LDS + c] = bv[u];
+                        sD[r * CH_LDS + c] = dv[u];
+                        any |= !(bv[u] == 0.0);
+                    }
+                    any = __syncthreads_or(any);
+                    if (threadIdx.x == 0) nz[(size_t)i * nb + k] = (unsigned char)(any != 0);
+                    if (any) {
+                        block_xyT<0>(sC, sB, sL);         // sB = L_kk^-1, left there by factor_and_commit(k)
+                        __syncthreads();
+                        store_block(sL, A, ld, i * CH_NB, k * CH_NB);
+                        CH_TICK(1);
+                        block_xyT<1>(sL, sL, sD);         // A_{k+1,k+1} -= L_{k+1,k} L_{k+1,k}^T, kept in shared memory
+                    }
+                    __syncthreads();
+                    if (threadIdx.x == 0) {
+                        __threadfence();                  // block (k+1,k) and its flag before the announcement; the
+                        atomicExch(ready, (unsigned)(k + 1));   // stores drained while the product above ran
+                    }
+                    factor_and_commit(k + 1, sD);
+                    CH_TICK(3);
+                }
+            } else {
+                // ---- phase 1: block-rows k+2 .. nb (nb = right-hand side) over CTAs 1 .. G-1; at the last
+                // panel block-row k+1 IS the right-hand side and belongs here too ----
+                const int first = (k + 1 < nb ? k + 2 : k + 1) + (cta - 1);
+                if (first <= nb) {
+                    constexpr int PER = CH_NB * CH_NB / CH_THREADS;       // 9
+                    double lv[PER], bv[PER];
+                    int i = first;
+#pragma unroll
+                    for (int u = 0; u < PER; ++u) lv[u] = Linv_ws[(size_t)k * CH_NB * CH_NB + threadIdx.x + u * CH_THREADS];
+#pragma unroll
+                    for (int u = 0; u < PER; ++u) {
+                        const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                        bv[u] = A[(size_t)(i * CH_NB + r) * ld + k * CH_NB + c];
+                    }
+#pragma unroll
+                    for (int u = 0; u < PER; ++u) {
+                        const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                        sB[r * CH_LDS + c] = lv[u];
+                    }
+                    for (; i <= nb; i += (int)P) {
+                        int any = 0;
+#pragma unroll
+                        for (int u = 0; u < PER; ++u) {
+                            const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                            sC[r * CH_LDS + c] = bv[u];
+                            any |= !(bv[u] == 0.0);
+                        }
+                        if (i + (int)P <= nb) {
+#pragma unroll
+                            for (int u = 0; u < PER; ++u) {
+                                const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                                bv[u] = A[(size_t)((i + (int)P) * CH_NB + r) * ld + k * CH_NB + c];
+                            }
+                        }
+                        any = __syncthreads_or(any);
+                        if (threadIdx.x == 0) nz[(size_t)i * nb + k] = (unsigned char)(any != 0);
+                        if (any) {
+                            block_xyT<0>(sC, sB, sL);
+                            __syncthreads();
+                            store_block(sL, A, ld, i * CH_NB, k * CH_NB);
+                        }
+                        __syncthreads();
                     }
                 }
-                any = __syncthreads_or(any);
-                if (threadIdx.x == 0) nz[(size_t)i * nb + k] = (unsigned char)(any != 0);
-                if (any) {                        // an exactly zero block stays zero
-                    // X = A_ik L^-T : X[r][c] = sum_m A_ik[r][m] Linv[c][m]
-                    block_xyT<0>(sC, sB, sL);
+                // barrier of CTAs 1 .. G-1 (monotone counter), then CTA 0's block (k+1,k)
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    __threadfence();
+                    atomicAdd(bar_ctr, 1u);
+                    const unsigned target = P * (unsigned)(k + 1);
+                    while (*(volatile unsigned *)bar_ctr < target) { }
+                    if (k + 1 < nb)
+                        while (*(volatile unsigned *)ready < (unsigned)(k + 1)) { }
+                    __threadfence();                      // acquire; also drops this SM's stale L1 lines
+                }
+                __syncthreads();
+                // ---- phase 2: trailing update, block (k+1,k+1) excluded (CTA 0 has it) ----
+                const int m = nb - 1 - k;
+                if (m >= CH_SUPER_MIN) {
+                    if (!sparse_tile_phase(sm, A, ld, nz, k, nb, cta, G))
+                        supertile_phase<DMMA>(sm, A, ld, nz, k, nb, cta, G, factor_and_commit);
+                } else if (m > 0) {
+                    const int ntiles = m * (m + 1) / 2 + m;
+                    for (int t = cta; t < ntiles; t += (int)P) {          // t = 0 is block (k+1,k+1)
+                        int ip, jp;
+                        if (t < m * (m + 1) / 2) {
+                            ip = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
+                            while ((ip + 1) * (ip + 2) / 2 <= t) ++ip;
+                            while (ip * (ip + 1) / 2 > t) --ip;
+                            jp = t - ip * (ip + 1) / 2;
+                        } else {
+                            ip = m;
+                            jp = t - m * (m + 1) / 2;
+                        }
+                        const int i = k + 1 + ip, j = k + 1 + jp;
+                        __syncthreads();
+                        load_block(sL, A, ld, i * CH_NB, k * CH_NB);
+                        load_block(sB, A, ld, j * CH_NB, k * CH_NB);
+                        load_block(sC, A, ld, i * CH_NB, j * CH_NB);
+                        __syncthreads();
+                        block_xyT<1>(sL, sB, sC);
+                        __syncthreads();
+                        store_block(sC, A, ld, i * CH_NB, j * CH_NB);
+                    }
+                }
+            }
+            grid.sync();
+            CH_TICK(4);
+        }
+    } else {
+        for (int k = 0; k < nb; ++k) {
+            // ---- phase 1: panel solve A_ik <- A_ik L_kk^-T with the inverse committed one phase earlier ----
+            const int rows_below = nb - k;            // block-rows k+1 .. nb (nb = RHS)
+            if (cta < rows_below) {
+                // the inverse and the first block of this CTA are requested together (18 independent loads per
+                // thread, one L2 round trip) before anything is parked in shared memory
+                constexpr int PER = CH_NB * CH_NB / CH_THREADS;       // 9
+                double lv[PER], bv[PER];
+                int i = k + 1 + cta;
+    #pragma unroll
+                for (int u = 0; u < PER; ++u) lv[u] = Linv_ws[(size_t)k * CH_NB * CH_NB + threadIdx.x + u * CH_THREADS];
+    #pragma unroll
+                for (int u = 0; u < PER; ++u) {
+                    const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                    bv[u] = A[(size_t)(i * CH_NB + r) * ld + k * CH_NB + c];
+                }
+    #pragma unroll
+                for (int u = 0; u < PER; ++u) {
+                    const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                    sB[r * CH_LDS + c] = lv[u];
+                }
+                for (; i <= nb; i += G) {
+                    int any = 0;
+    #pragma unroll
+                    for (int u = 0; u < PER; ++u) {
+                        const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                        sC[r * CH_LDS + c] = bv[u];
+                        any |= !(bv[u] == 0.0);
+                    }
+                    if (i + G <= nb) {                // next block of this CTA (only when rows outnumber CTAs)
+    #pragma unroll
+                        for (int u = 0; u < PER; ++u) {
+                            const int e = threadIdx.x + u * CH_THREADS, r = e / CH_NB, c = e - r * CH_NB;
+                            bv[u] = A[(size_t)((i + G) * CH_NB + r) * ld + k * CH_NB + c];
+                        }
+                    }
+                    any = __syncthreads_or(any);
+                    if (threadIdx.x == 0) nz[(size_t)i * nb + k] = (unsigned char)(any != 0);
+                    if (any) {                        // an exactly zero block stays zero
+                        // X = A_ik L^-T : X[r][c] = sum_m A_ik[r][m] Linv[c][m]
+                        block_xyT<0>(sC, sB, sL);
+                        __syncthreads();
+                        store_block(sL, A, ld, i * CH_NB, k * CH_NB);
+                    }
+                    __syncthreads();                  // sC / sL are rewritten by the next block
+                }
+            }
+            CH_TICK(1);
+            grid.sync();
+            CH_TICK(2);
+            // ---- phase 2: trailing update over tiles (i, j), k < j <= i <= nb, j < nb. Look-ahead: the CTA
+            // that updates the tile holding the next diagonal block (tile 0 = CTA 0) factors that block
+            // right away, so the factor overlaps the rest of the update instead of heading phase 1. ----
+            const int m = nb - 1 - k;                 // remaining diagonal blocks
+            if (m >= CH_SUPER_MIN) {
+                // 96 x 96 super-tiles over the trailing block rows k+1 .. nb, aligned to even block indices
+                if (G == 1 || cta == 0 || !sparse_tile_phase(sm, A, ld, nz, k, nb, cta, G))
+                    supertile_phase<DMMA>(sm, A, ld, nz, k, nb, cta, G, factor_and_commit);
+            } else if (m > 0) {
+                // tiles: for j' in [0, m): i' in [j', m]  (i' == m is the RHS block-row)
+                const int ntiles = m * (m + 1) / 2 + m;
+                for (int t = st_first_tile(cta, G); t < ntiles; t = st_next_tile(t, cta, G)) {
+                    int ip, jp;
+                    if (t < m * (m + 1) / 2) {
+                        // lower triangle of an m x m block matrix, row-major enumeration
+                        ip = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
+                        while ((ip + 1) * (ip + 2) / 2 <= t) ++ip;
+                        while (ip * (ip + 1) / 2 > t) --ip;
+                        jp = t - ip * (ip + 1) / 2;
+                    } else {
+                        ip = m;
+                        jp = t - m * (m + 1) / 2;
+                    }
+                    const int i = k + 1 + ip, j = k + 1 + jp;
                     __syncthreads();
-                    store_block(sL, A, ld, i * CH_NB, k * CH_NB);
-                }
-                __syncthreads();                  // sC / sL are rewritten by the next block
-            }
-        }
-        CH_TICK(1);
-        grid.sync();
-        CH_TICK(2);
-        // ---- phase 2: trailing update over tiles (i, j), k < j <= i <= nb, j < nb. Look-ahead: the CTA
-        // that updates the tile holding the next diagonal block (tile 0 = CTA 0) factors that block
-        // right away, so the factor overlaps the rest of the update instead of heading phase 1. ----
-        const int m = nb - 1 - k;                 // remaining diagonal blocks
-        if (m >= CH_SUPER_MIN) {
-            // 96 x 96 super-tiles over the trailing block rows k+1 .. nb, aligned to even block indices
-            if (G == 1 || cta == 0 || !sparse_tile_phase(sm, A, ld, nz, k, nb, cta, G))
-                supertile_phase<DMMA>(sm, A, ld, nz, k, nb, cta, G, factor_and_commit);
-        } else if (m > 0) {
-            // tiles: for j' in [0, m): i' in [j', m]  (i' == m is the RHS block-row)
-            const int ntiles = m * (m + 1) / 2 + m;
-            for (int t = st_first_tile(cta, G); t < ntiles; t = st_next_tile(t, cta, G)) {
-                int ip, jp;
-                if (t < m * (m + 1) / 2) {
-                    // lower triangle of an m x m block matrix, row-major enumeration
-                    ip = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
-                    while ((ip + 1) * (ip + 2) / 2 <= t) ++ip;
-                    while (ip * (ip + 1) / 2 > t) --ip;
-                    jp = t - ip * (ip + 1) / 2;
-                } else {
-                    ip = m;
-                    jp = t - m * (m + 1) / 2;
-                }
-                const int i = k + 1 + ip, j = k + 1 + jp;
-                __syncthreads();
-                load_block(sL, A, ld, i * CH_NB, k * CH_NB);
-                load_block(sB, A, ld, j * CH_NB, k * CH_NB);
-                load_block(sC, A, ld, i * CH_NB, j * CH_NB);
-                __syncthreads();
-                block_xyT<1>(sL, sB, sC);
-                __syncthreads();
-                store_block(sC, A, ld, i * CH_NB, j * CH_NB);
-                if (t == 0) {
-                    CH_TICK(3);
-                    factor_and_commit(k + 1);
-                    CH_TICK(0);
+                    load_block(sL, A, ld, i * CH_NB, k * CH_NB);
+                    load_block(sB, A, ld, j * CH_NB, k * CH_NB);
+                    load_block(sC, A, ld, i * CH_NB, j * CH_NB);
+                    __syncthreads();
+                    block_xyT<1>(sL, sB, sC);
+                    __syncthreads();
+                    store_block(sC, A, ld, i * CH_NB, j * CH_NB);
+                    if (t == 0) {
+                        CH_TICK(3);
+                        factor_and_commit(k + 1);
+                        CH_TICK(0);
+                    }
                 }
             }
+            CH_TICK(3);
+            grid.sync();
+            CH_TICK(4);
         }
-        CH_TICK(3);
-        grid.sync();
-        CH_TICK(4);
+
     }
 
     // ---- backward substitution L^T x = y, y = first row of the RHS block-row ----
@@ -881,6 +1028,11 @@ int chol_solve_launch(double *A, size_t ld, int npad, double *d_Linv, double *d_
     // no point in more CTAs than the widest phase can use
     int need = nb * (nb + 1) / 2 + nb + 1;
     if (G > need) G = need;
+    {   // barrier counter + `ready` of the critical-path form, in the slack behind K11's block flags
+        unsigned char *nzp = reinterpret_cast<unsigned char *>(d_Linv + (size_t)nb * CH_NB * CH_NB);
+        void *syncw = nzp + (((size_t)(nb + 1) * nb + 15) & ~(size_t)15);
+        if (cudaMemsetAsync(syncw, 0, 16, st) != cudaSuccess) return SFM_E_CUDA;
+    }
     void *args[] = {&A, &ld, &nb, &d_Linv, &d_x, &d_fail, &d_prof};
     const void *fn = chol_use_dmma() ? (const void *)chol_solve_kernel<true> : (const void *)chol_solve_kernel<false>;
     cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(G), dim3(CH_THREADS), args, sizeof(CholSmem), st);
@@ -915,7 +1067,7 @@ extern "C" size_t sfm_chol_solve_workspace_bytes(int32_t n) {
     size_t npad = (size_t)ceil_div(n, CH_NB) * CH_NB;
     size_t bytes = (npad + CH_NB) * npad * sizeof(double);              // A
     bytes += (npad / CH_NB) * (size_t)CH_NB * CH_NB * sizeof(double);    // Linv
-    bytes += align_up((npad / CH_NB + 1) * (npad / CH_NB), 256);        // block non-zero flags
+    bytes += align_up((npad / CH_NB + 1) * (npad / CH_NB) + 32, 256);   // block non-zero flags + K11's sync words
     bytes += npad * sizeof(double) + 256;                                // x, flag
     return bytes;
 }
@@ -929,7 +1081,7 @@ static int chol_solve_impl(const double *d_S, const double *d_g, int32_t n, doub
     size_t ld = (size_t)npad;
     double *A = reinterpret_cast<double *>(d_ws);
     double *Linv = A + (size_t)(npad + CH_NB) * ld;
-    double *x = Linv + (size_t)(npad / CH_NB) * CH_NB * CH_NB + align_up((size_t)(npad / CH_NB + 1) * (npad / CH_NB), 256) / sizeof(double);
+    double *x = Linv + (size_t)(npad / CH_NB) * CH_NB * CH_NB + align_up((size_t)(npad / CH_NB + 1) * (npad / CH_NB) + 32, 256) / sizeof(double);
     int *flag = reinterpret_cast<int *>(x + npad);
     SFM_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), st));
     chol_pack_kernel<<<sm_count() * 4, 256, 0, st>>>(d_S, d_g, n, npad, ld, A);
