@@ -940,46 +940,67 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
     // the ~10 non-zero blocks of a block column from L2 fast enough -- 5.7 us per step against 4.3 us for
     // the grid-wide steps below at C5 -- so the grid-wide form serves sparse and dense factors alike.)
     for (int e = cta * CH_THREADS + threadIdx.x; e < nb * CH_NB; e += G * CH_THREADS) x_out[e] = yrow[e];
-    grid.sync();
-    for (int k = nb - 1; k >= 0; --k) {
-        // every CTA: x_k = Linv_kk^T y_k  (48 x 48 mat-vec from global Linv)
-        __syncthreads();
-        if (threadIdx.x < CH_NB) sm.x[threadIdx.x] = x_out[k * CH_NB + threadIdx.x];
-        __syncthreads();
-        {
+    {
+        // Everything a step reads except x itself is final before the loop starts: the inverse of the
+        // diagonal block and this CTA's first block L_kb of the step are requested one step ahead, before
+        // the grid barrier, so a step's chain is load x -> two 48 x 48 mat-vecs -> barrier.
+        const int c = threadIdx.x & 63, part = threadIdx.x >> 6;
+        double li[12], lb[12];
+        int have_b = 0;
+        auto prefetch = [&](int k) {
             const double *Li = Linv_ws + (size_t)k * CH_NB * CH_NB;
-            const int c = threadIdx.x & 63, part = threadIdx.x >> 6;
-            double s = 0.0;
-            if (c < CH_NB)
-#pragma unroll 4
-                for (int r = part * 12; r < part * 12 + 12; ++r)
-                    if (r >= c) s += Li[r * CH_NB + c] * sm.x[r];
-            sC[part * 64 + c] = s;
-        }
-        __syncthreads();
-        if (threadIdx.x < CH_NB)
-            sB[threadIdx.x] = sC[threadIdx.x] + sC[64 + threadIdx.x] + sC[128 + threadIdx.x] +
-                                sC[192 + threadIdx.x];
-        __syncthreads();
-        // y_b -= L_kb^T x_k for b < k: (block, quarter of the rows) pairs round-robin over CTAs would
-        // need atomics; instead each CTA takes whole column blocks, 4 row-quarters per thread group
-        for (int b = cta; b < k; b += G) {
-            if (!nz[(size_t)k * nb + b]) continue;          // zero block: no contribution (CTA-uniform)
-            const int c = threadIdx.x & 63, part = threadIdx.x >> 6;
-            double s = 0.0;
-            if (c < CH_NB)
-#pragma unroll 4
-                for (int r = part * 12; r < part * 12 + 12; ++r)
-                    s += A[(size_t)(k * CH_NB + r) * ld + b * CH_NB + c] * sB[r];
+#pragma unroll
+            for (int r = 0; r < 12; ++r) li[r] = (c < CH_NB) ? Li[(part * 12 + r) * CH_NB + c] : 0.0;
+            have_b = (cta < k) && nz[(size_t)k * nb + cta];
+            if (have_b) {
+#pragma unroll
+                for (int r = 0; r < 12; ++r)
+                    lb[r] = (c < CH_NB) ? A[(size_t)(k * CH_NB + part * 12 + r) * ld + cta * CH_NB + c] : 0.0;
+            }
+        };
+        prefetch(nb - 1);
+        grid.sync();
+        for (int k = nb - 1; k >= 0; --k) {
+            // every CTA: x_k = Linv_kk^T y_k
             __syncthreads();
-            sC[part * 64 + c] = s;
+            if (threadIdx.x < CH_NB) sm.x[threadIdx.x] = x_out[k * CH_NB + threadIdx.x];
+            __syncthreads();
+            {
+                double s = 0.0;
+#pragma unroll
+                for (int r = 0; r < 12; ++r)
+                    if (part * 12 + r >= c) s += li[r] * sm.x[part * 12 + r];
+                sC[part * 64 + c] = s;
+            }
             __syncthreads();
             if (threadIdx.x < CH_NB)
-                x_out[b * CH_NB + threadIdx.x] -= sC[threadIdx.x] + sC[64 + threadIdx.x] +
-                                                  sC[128 + threadIdx.x] + sC[192 + threadIdx.x];
+                sB[threadIdx.x] = sC[threadIdx.x] + sC[64 + threadIdx.x] + sC[128 + threadIdx.x] +
+                                    sC[192 + threadIdx.x];
+            __syncthreads();
+            // y_b -= L_kb^T x_k for b < k: each CTA takes whole column blocks (no atomics)
+            for (int b = cta; b < k; b += G) {
+                const bool mine = (b == cta);
+                if (mine ? !have_b : !nz[(size_t)k * nb + b]) continue;      // zero block (CTA-uniform)
+                double s = 0.0;
+                if (mine) {
+#pragma unroll
+                    for (int r = 0; r < 12; ++r) s += lb[r] * sB[part * 12 + r];
+                } else if (c < CH_NB) {
+#pragma unroll 4
+                    for (int r = part * 12; r < part * 12 + 12; ++r)
+                        s += A[(size_t)(k * CH_NB + r) * ld + b * CH_NB + c] * sB[r];
+                }
+                __syncthreads();
+                sC[part * 64 + c] = s;
+                __syncthreads();
+                if (threadIdx.x < CH_NB)
+                    x_out[b * CH_NB + threadIdx.x] -= sC[threadIdx.x] + sC[64 + threadIdx.x] +
+                                                      sC[128 + threadIdx.x] + sC[192 + threadIdx.x];
+            }
+            if (k > 0) prefetch(k - 1);
+            grid.sync();
+            if (cta == 0 && threadIdx.x < CH_NB) x_out[k * CH_NB + threadIdx.x] = sB[threadIdx.x];
         }
-        grid.sync();
-        if (cta == 0 && threadIdx.x < CH_NB) x_out[k * CH_NB + threadIdx.x] = sB[threadIdx.x];
     }
     CH_TICK(5);
 #undef CH_TICK
