@@ -99,3 +99,26 @@ def test_stream_replayer_chunks_equal_the_reference_stream():
     rep.finish()
     assert off == total and np.array_equal(out, ref)
     assert random.getstate() == state_ref
+
+
+def test_sample_stream_property_random_shapes():
+    """Property test of the bulk replay against CPython itself: random population sizes (both branches of
+    random.sample), sample sizes, counts and starting offsets inside a 624-word generation."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=60, deadline=None)
+    @given(n=st.integers(1, 70000), k=st.integers(1, 12), count=st.integers(16, 400), off=st.integers(0, 1300),
+           seed=st.integers(0, 2 ** 31 - 1))
+    def check(n, k, count, off, seed):
+        k = min(k, n)
+        random.seed(seed)
+        [random.getrandbits(32) for _ in range(off)]
+        a = np.array([random.sample(range(n), k) for _ in range(count)])
+        after_a = random.random()
+        random.seed(seed)
+        [random.getrandbits(32) for _ in range(off)]
+        b = sampler.sample_stream(n, k, count)
+        assert np.array_equal(a, b), (n, k, count, off)
+        assert after_a == random.random(), (n, k, count, off)
+
+    check()
