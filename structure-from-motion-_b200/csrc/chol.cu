@@ -403,6 +403,41 @@ __device__ __forceinline__ void dmma_884(double &d0, double &d1, double a, doubl
                  : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
+// block_xyT on the FP64 tensor path: warp w < 6 owns rows 8w .. 8w+7 of C (six 8 x 8 tiles), one A and six B
+// fragment loads (conflict-free at the row stride of 52) for six DMMAs per k-step. The scalar form above issues
+// 288 LDS.64 and 432 DFMAs per thread and takes ~2 us per 48 x 48 x 48 product; two of them sit on CTA 0's chain
+// of every panel.
+template <int MODE>
+__device__ __forceinline__ void block_xyT_mma(const double *X, const double *Y, double *C) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp >= 6) return;
+    const int g = lane >> 2, q = lane & 3;
+    double acc[6][2];
+    double *pc = C + (8 * warp + g) * CH_LDS + 2 * q;
+#pragma unroll
+    for (int t = 0; t < 6; ++t) {
+        if (MODE == 0) {
+            acc[t][0] = 0.0; acc[t][1] = 0.0;
+        } else {
+            const double2 v = *reinterpret_cast<const double2 *>(pc + 8 * t);
+            acc[t][0] = v.x; acc[t][1] = v.y;
+        }
+    }
+    const double *pa = X + (8 * warp + g) * CH_LDS + q;
+    const double *pb = Y + g * CH_LDS + q;
+#pragma unroll 4
+    for (int k4 = 0; k4 < CH_NB; k4 += 4) {
+        const double a = (MODE == 0) ? pa[k4] : -pa[k4];
+        double bf[6];
+#pragma unroll
+        for (int t = 0; t < 6; ++t) bf[t] = pb[8 * t * CH_LDS + k4];
+#pragma unroll
+        for (int t = 0; t < 6; ++t) dmma_884(acc[t][0], acc[t][1], a, bf[t]);
+    }
+#pragma unroll
+    for (int t = 0; t < 6; ++t) *reinterpret_cast<double2 *>(pc + 8 * t) = make_double2(acc[t][0], acc[t][1]);
+}
+
 // Phase-2 work split (G > 1): CTA 0 is the critical path -- it updates ONLY the next diagonal block
 // (one 48 x 48 product with the block it solved in phase 1) and factors it right away; the
 // super-tiles, with that block masked out of tile 0, go round-robin over CTAs 1 .. G-1. (CTA 0 used
@@ -697,11 +732,13 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
                     any = __syncthreads_or(any);
                     if (threadIdx.x == 0) nz[(size_t)i * nb + k] = (unsigned char)(any != 0);
                     if (any) {
-                        block_xyT<0>(sC, sB, sL);         // sB = L_kk^-1, left there by factor_and_commit(k)
+                        // sB = L_kk^-1, left there by factor_and_commit(k)
+                        if (DMMA) block_xyT_mma<0>(sC, sB, sL); else block_xyT<0>(sC, sB, sL);
                         __syncthreads();
                         store_block(sL, A, ld, i * CH_NB, k * CH_NB);
                         CH_TICK(1);
-                        block_xyT<1>(sL, sL, sD);         // A_{k+1,k+1} -= L_{k+1,k} L_{k+1,k}^T, kept in shared memory
+                        // A_{k+1,k+1} -= L_{k+1,k} L_{k+1,k}^T, kept in shared memory
+                        if (DMMA) block_xyT_mma<1>(sL, sL, sD); else block_xyT<1>(sL, sL, sD);
                     }
                     __syncthreads();
                     if (threadIdx.x == 0) {
@@ -749,7 +786,7 @@ chol_solve_kernel(double *__restrict__ A, size_t ld, int nb, double *__restrict_
                         any = __syncthreads_or(any);
                         if (threadIdx.x == 0) nz[(size_t)i * nb + k] = (unsigned char)(any != 0);
                         if (any) {
-                            block_xyT<0>(sC, sB, sL);
+                            if (DMMA) block_xyT_mma<0>(sC, sB, sL); else block_xyT<0>(sC, sB, sL);
                             __syncthreads();
                             store_block(sL, A, ld, i * CH_NB, k * CH_NB);
                         }
