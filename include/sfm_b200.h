@@ -182,6 +182,13 @@ typedef struct sfm_ba_result {
 
 void sfm_ba_default_options(sfm_ba_options *opts);
 size_t sfm_ba_workspace_bytes(int32_t n_cams, int32_t n_pts, int32_t n_obs);
+/* Everything sfm_ba_solve* needs lives in the caller's workspace except the plan-time pair list of the
+ * gather-form Schur complement (12 B per pair of observations of one point), which the library keeps in
+ * stream-ordered allocations cached per workspace pointer (at most 16 entries, replaced / evicted
+ * automatically). This releases all of them on `stream` (e.g. before handing the device to another
+ * library); the next solve rebuilds what it needs. Returns the number of bytes released through *bytes
+ * (may be NULL). */
+int sfm_ba_release_cache(uint64_t *bytes, void *stream);
 
 /* K8 alone: residual vector of bundle_adjustment_residuals (BundleAdjustment.py:43-110),
  * d_r [n_obs,2] interleaved [du,dv] = observed - projected (may be null), d_cost[0] = 0.5 |r|^2

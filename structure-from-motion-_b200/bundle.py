@@ -95,6 +95,14 @@ class BAProblem:
                     n_linearisations=res.n_linearisations, n_trials=res.n_trials, n_chol_fail=res.n_chol_fail)
 
 
+def release_cache() -> int:
+    """Free the plan-time pair lists the library caches per workspace (sfm_ba_release_cache); returns the bytes."""
+    import ctypes as C
+    n = C.c_uint64(0)
+    _lib.check(_lib.load().sfm_ba_release_cache(C.addressof(n), device.stream()), "sfm_ba_release_cache")
+    return int(n.value)
+
+
 def ba_solve_sparse(cams, pts, cam_idx, pt_idx, obs, K, max_nfev=BA_MAX_NFEV, tol=REF_TOL, verbose=False):
     """Host arrays in/out: cams [Nc,6] = [rotvec, t], pts [Np,3] -> (cams, pts, info)."""
     cams = np.ascontiguousarray(cams, np.float64).reshape(-1, 6)

@@ -1840,6 +1840,20 @@ static int ba_acquire_index(BAPlan &pl, bool reuse, const void *d_ws, const doub
     return SFM_OK;
 }
 
+extern "C" int sfm_ba_release_cache(uint64_t *bytes, void *stream) {
+    cudaStream_t st = as_stream(stream);
+    std::lock_guard<std::mutex> g(g_plan_mu);
+    uint64_t total = 0;
+    for (PlanKey &q : g_plans) {
+        if (q.pair_keys) { SFM_CUDA_TRY(cudaFreeAsync(q.pair_keys, st)); total += sizeof(uint32_t) * (uint64_t)q.npairs; }
+        if (q.pair_vals) { SFM_CUDA_TRY(cudaFreeAsync(q.pair_vals, st)); total += sizeof(uint2) * (uint64_t)q.npairs; }
+        q.pair_keys = nullptr; q.pair_vals = nullptr; q.npairs = 0;
+    }
+    g_plans.clear();                    // index structures in the workspaces are rebuilt on the next solve
+    if (bytes) *bytes = total;
+    return SFM_OK;
+}
+
 static int ba_prepare(BAPlan &pl, void *d_ws, size_t ws_bytes, int32_t n_cams, int32_t n_pts, int32_t n_obs) {
     if (n_cams < 1 || n_pts < 1 || n_obs < 1 || !d_ws) return SFM_E_INVALID;
     unsigned char *base = reinterpret_cast<unsigned char *>(align_up((size_t)d_ws, 256));

@@ -253,3 +253,19 @@ def test_schur_pair_list_equals_atomic_path(cuda_device, monkeypatch):
     assert ia["n_trials"] == ib["n_trials"] and ia["status"] == ib["status"]
     assert abs(ia["cost"] - ib["cost"]) / ia["cost"] < 1e-10
     assert rel_err(cb, ca) < 1e-7 and rel_err(pb, pa) < 1e-7
+
+
+def test_release_cache_frees_pair_lists_and_solves_again(cuda_device, monkeypatch):
+    """sfm_ba_release_cache drops the cached pair lists (reported in bytes); the next solve rebuilds them and
+    returns the same result."""
+    from sfm_b200 import bundle, scenes
+    monkeypatch.setenv("SFM_SCHUR_PAIRS_MIN", "0")
+    sc = scenes.ba_scene(n_cams=10, n_pts=400, obs_per_pt=5, seed=3)
+    cams0, pts0 = _x0(sc)
+    bundle.release_cache()
+    c1, p1, i1 = bundle.ba_solve_sparse(cams0, pts0, sc["cam_idx"], sc["pt_idx"], sc["obs"], sc["K"])
+    freed = bundle.release_cache()
+    assert freed >= 12 * 400 * 15                      # 15 pairs per point, 12 B each, before padding
+    assert bundle.release_cache() == 0
+    c2, p2, i2 = bundle.ba_solve_sparse(cams0, pts0, sc["cam_idx"], sc["pt_idx"], sc["obs"], sc["K"])
+    assert i1["n_trials"] == i2["n_trials"] and abs(i1["cost"] - i2["cost"]) <= 1e-12 * i1["cost"]
