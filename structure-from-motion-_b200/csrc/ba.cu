@@ -368,20 +368,33 @@ ba_camera_pass_kernel(KParam K, const double *__restrict__ camlin, const double 
 }
 
 // Sum the chunk partials of every camera in chunk order -> U [nc,21], g_c [nc,6] (this rank's share).
-__global__ void ba_cam_finalize_kernel(const double *__restrict__ Upart, const int32_t *__restrict__ chunk_ptr,
-                                       int nc, double *__restrict__ U, double *__restrict__ gc) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= nc) return;
-    double acc[27];
+// Warp per camera, lane = one of the 27 partial-sum slots (U 21 | g_c 6), chunks added in order (the same
+// fixed summation order as ever). Single GPU (Dc != nullptr): U and g_c are final here, so the MINPACK
+// scaling of ba_cam_scale_kernel is done in the same launch from the values the lanes already hold.
+__global__ void __launch_bounds__(256)
+ba_cam_finalize_kernel(const double *__restrict__ Upart, const int32_t *__restrict__ chunk_ptr, int nc,
+                       double *__restrict__ U, double *__restrict__ gc, int first, double *__restrict__ Dc,
+                       unsigned long long *__restrict__ gmax) {
+    const int c = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (c >= nc) return;                                   // warp-uniform
+    double v = 0.0;
+    if (lane < 27)
+        for (int ch = chunk_ptr[c]; ch < chunk_ptr[c + 1]; ++ch) v += Upart[(size_t)ch * 27 + lane];
+    if (lane < 21) U[(size_t)c * 21 + lane] = v;
+    else if (lane < 27) gc[(size_t)c * 6 + (lane - 21)] = v;
+    if (!Dc) return;
+    const int j = lane < 6 ? lane : 0;
+    const double ujj = __shfl_sync(0xffffffffu, v, sym_idx(j, j)), gj = __shfl_sync(0xffffffffu, v, 21 + j);
+    double gm = 0.0;
+    if (lane < 6) {
+        const double cn = sqrt(ujj);
+        const double d = first ? (cn == 0.0 ? 1.0 : cn) : fmax(Dc[(size_t)c * 6 + lane], cn);
+        Dc[(size_t)c * 6 + lane] = d;
+        if (cn > 0.0) gm = fabs(gj) / cn;
+    }
 #pragma unroll
-    for (int i = 0; i < 27; ++i) acc[i] = 0.0;
-    for (int ch = chunk_ptr[c]; ch < chunk_ptr[c + 1]; ++ch)
-#pragma unroll
-        for (int i = 0; i < 27; ++i) acc[i] += Upart[(size_t)ch * 27 + i];
-#pragma unroll
-    for (int i = 0; i < 21; ++i) U[(size_t)c * 21 + i] = acc[i];
-#pragma unroll
-    for (int j = 0; j < 6; ++j) gc[(size_t)c * 6 + j] = acc[21 + j];
+    for (int o = 4; o > 0; o >>= 1) gm = fmax(gm, __shfl_xor_sync(0xffffffffu, gm, o));
+    if (lane == 0) atomic_max_pos(gmax, gm);
 }
 
 // From the (all-rank) U, g_c: the MINPACK scaling Dc (first linearisation: column norm, 1 if zero;
@@ -1991,13 +2004,17 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
                                                               pl.chunk_cam, pl.chunk_beg, pl.chunk_end, pl.Upart);
             SFM_LAUNCH_CHECK();
         }
-        ba_cam_finalize_kernel<<<ceil_div(nc, 128), 128, 0, st>>>(pl.Upart, pl.chunk_ptr, nc, pl.U, pl.gc);
+        // single GPU: the camera scaling rides in the finalize launch; multi-GPU: it needs the all-reduced U, g_c
+        ba_cam_finalize_kernel<<<ceil_div(nc, 8), 256, 0, st>>>(pl.Upart, pl.chunk_ptr, nc, pl.U, pl.gc, first,
+                                                               comm ? nullptr : pl.Dc, pl.gmax);
         SFM_LAUNCH_CHECK();
         ba_reduce_scalars_kernel<<<1, 256, 0, st>>>(pl.costpart, pl.grid_obs, nullptr, 0, nullptr, nullptr, nullptr, pl.red1);
         SFM_LAUNCH_CHECK();
-        if ((r = comm_allreduce_sum_f64(comm, pl.U, 27 * (size_t)nc + 1, st)) != SFM_OK) return r;
-        ba_cam_scale_kernel<<<ceil_div(nc, 128), 128, 0, st>>>(pl.U, pl.gc, nc, first, pl.Dc, pl.gmax);
-        SFM_LAUNCH_CHECK();
+        if (comm) {
+            if ((r = comm_allreduce_sum_f64(comm, pl.U, 27 * (size_t)nc + 1, st)) != SFM_OK) return r;
+            ba_cam_scale_kernel<<<ceil_div(nc, 128), 128, 0, st>>>(pl.U, pl.gc, nc, first, pl.Dc, pl.gmax);
+            SFM_LAUNCH_CHECK();
+        }
         return SFM_OK;
     };
 
@@ -2252,9 +2269,8 @@ extern "C" int sfm_ba_linearise(const double *d_cam, const double *d_pts, const 
                                                               pl.chunk_beg, pl.chunk_end, pl.Upart);
             SFM_LAUNCH_CHECK();
         }
-        ba_cam_finalize_kernel<<<ceil_div(pl.nc, 128), 128, 0, st>>>(pl.Upart, pl.chunk_ptr, pl.nc, pl.U, pl.gc);
-        SFM_LAUNCH_CHECK();
-        ba_cam_scale_kernel<<<ceil_div(pl.nc, 128), 128, 0, st>>>(pl.U, pl.gc, pl.nc, 1, pl.Dc, pl.gmax);
+        ba_cam_finalize_kernel<<<ceil_div(pl.nc, 8), 256, 0, st>>>(pl.Upart, pl.chunk_ptr, pl.nc, pl.U, pl.gc, 1, pl.Dc,
+                                                                  pl.gmax);
         SFM_LAUNCH_CHECK();
     }
     if (which & 4) {
