@@ -1995,25 +1995,44 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
     static thread_local double *h_scal = nullptr;
     if (!h_scal) SFM_CUDA_TRY(cudaMallocHost(&h_scal, 16 * sizeof(double)));
 
+    // Single GPU: the camera pass (K9c + finalize/scale) and the point pass (K9p) touch disjoint outputs, so the
+    // camera pass runs on a side stream forked from / joined to the caller's stream with events -- at C3 both
+    // are ~14 us kernels that fill a fraction of the GPU. (Multi-GPU keeps one stream: the all-reduce follows.)
+    static thread_local cudaStream_t side = nullptr;
+    static thread_local cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    if (!comm && !side) {
+        SFM_CUDA_TRY(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+        SFM_CUDA_TRY(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+        SFM_CUDA_TRY(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+    }
     auto linearise = [&](int first) -> int {
         int r;
         SFM_CUDA_TRY(cudaMemsetAsync(pl.gmax, 0, 8, st));
-        if ((r = launch_point_pass(pl, K, pl.camlin[cur], pl.pts[cur], obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return r;
+        cudaStream_t cs = st;                                  // stream of the camera pass
+        if (!comm) {
+            SFM_CUDA_TRY(cudaEventRecord(ev_fork, st));
+            SFM_CUDA_TRY(cudaStreamWaitEvent(side, ev_fork, 0));
+            cs = side;
+        }
         if (pl.nchunks) {
-            ba_camera_pass_kernel<<<pl.nchunks, K9C_THREADS, 0, st>>>(K, pl.camlin[cur], pl.pts[cur], pl.obs_c, pl.pt_c,
+            ba_camera_pass_kernel<<<pl.nchunks, K9C_THREADS, 0, cs>>>(K, pl.camlin[cur], pl.pts[cur], pl.obs_c, pl.pt_c,
                                                               pl.chunk_cam, pl.chunk_beg, pl.chunk_end, pl.Upart);
             SFM_LAUNCH_CHECK();
         }
         // single GPU: the camera scaling rides in the finalize launch; multi-GPU: it needs the all-reduced U, g_c
-        ba_cam_finalize_kernel<<<ceil_div(nc, 8), 256, 0, st>>>(pl.Upart, pl.chunk_ptr, nc, pl.U, pl.gc, first,
+        ba_cam_finalize_kernel<<<ceil_div(nc, 8), 256, 0, cs>>>(pl.Upart, pl.chunk_ptr, nc, pl.U, pl.gc, first,
                                                                comm ? nullptr : pl.Dc, pl.gmax);
         SFM_LAUNCH_CHECK();
+        if (!comm) SFM_CUDA_TRY(cudaEventRecord(ev_join, side));
+        if ((r = launch_point_pass(pl, K, pl.camlin[cur], pl.pts[cur], obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return r;
         ba_reduce_scalars_kernel<<<1, 256, 0, st>>>(pl.costpart, pl.grid_obs, nullptr, 0, nullptr, nullptr, nullptr, pl.red1);
         SFM_LAUNCH_CHECK();
         if (comm) {
             if ((r = comm_allreduce_sum_f64(comm, pl.U, 27 * (size_t)nc + 1, st)) != SFM_OK) return r;
             ba_cam_scale_kernel<<<ceil_div(nc, 128), 128, 0, st>>>(pl.U, pl.gc, nc, first, pl.Dc, pl.gmax);
             SFM_LAUNCH_CHECK();
+        } else {
+            SFM_CUDA_TRY(cudaStreamWaitEvent(st, ev_join, 0));
         }
         return SFM_OK;
     };
