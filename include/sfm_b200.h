@@ -246,6 +246,30 @@ size_t sfm_chol_solve_workspace_bytes(int32_t n);
 int sfm_chol_solve(const double *d_S, const double *d_g, int32_t n, double *d_x, int32_t *d_fail,
                    void *d_ws, size_t ws_bytes, void *stream);
 
+/* K11s: the same solve through the structure-aware kernel (csrc/chol_dag.cu): the 48 x 48 block pattern
+ * is read off the numeric zeros of d_S, analysed on the host (nested dissection, symbolic factorisation,
+ * static task schedule -- per problem, not per solve) and factored as a left-looking task graph whose chain
+ * is the height of the elimination tree instead of the number of panels. Host-synchronous.
+ *   order_mode 0 = pick the order with the shortest simulated schedule, 1 = natural, 2 = nested dissection
+ *   repeats    the factor + solve is launched this many times (timing); results of the last launch
+ *   d_fail[0]  1 = a pivot was not positive, 2 = an internal wait timed out (scheduling bug)
+ *   h_info[4]  optional HOST out: {order kind, elimination-tree height, off-diagonal L blocks, simulated us}
+ * Workspace as sfm_chol_solve. Replaces what MINPACK's dense QR does behind BundleAdjustment.py:205-212. */
+int sfm_chol_solve_structured(const double *d_S, const double *d_g, int32_t n, int32_t order_mode,
+                              int32_t repeats, double *d_x, int32_t *d_fail, void *d_ws, size_t ws_bytes,
+                              double *h_info, void *stream);
+
+/* The plan of K11s as plain HOST arrays (no device work): lets tests replay the task graph on a CPU-only
+ * box. h_pattern [nb,nb] (lower triangle, != 0 = block present). Call once with only h_sizes to size the
+ * arrays: h_sizes[9] = {off-diagonal L blocks, tasks, forward tasks, entries, order kind, tree height,
+ * len(fwd_list), len(bwd_list), partial-sum scratch blocks}; h_tasks rows are 12 int32 (type, j, i, dst,
+ * src_r, src_c, src_T, beg, end, pad x3), h_entries rows 4 int32 (a, b, t, pad), see csrc/chol_plan.h;
+ * *_ptr [n_ctas+1]. Any array pointer may be null. */
+int sfm_chol_plan_export(const uint8_t *h_pattern, int32_t nb, int32_t n_ctas, int32_t order_mode,
+                         int64_t *h_sizes, double *h_sim_us, int32_t *h_perm, int32_t *h_colptr,
+                         int32_t *h_rowidx, int32_t *h_tasks, int32_t *h_entries, int32_t *h_fwd_ptr,
+                         int32_t *h_fwd_list, int32_t *h_bwd_ptr, int32_t *h_bwd_list);
+
 /* Same solve with a per-phase time profile accumulated into d_phase_ns[6] (device, caller-zeroed;
  * nanoseconds seen by CTA 0: diagonal factor, panel solve, barrier 1, trailing update, barrier 2,
  * back substitution). Diagnostic entry point used by tools/chol_probe.py. */

@@ -78,6 +78,10 @@ SIGNATURES = {
                                    c_vp, C.c_int32, C.c_int32, c_vp, C.c_size_t, c_vp]),
     "sfm_chol_solve_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "sfm_chol_solve": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_i32p, c_vp, C.c_size_t, c_vp]),
+    "sfm_chol_solve_structured": (C.c_int, [c_f64p, c_f64p, C.c_int32, C.c_int32, C.c_int32, c_f64p, c_i32p, c_vp,
+                                            C.c_size_t, c_vp, c_vp]),
+    "sfm_chol_plan_export": (C.c_int, [c_vp, C.c_int32, C.c_int32, C.c_int32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                       c_vp, c_vp, c_vp, c_vp, c_vp]),
     "sfm_chol_diag_bench": (C.c_int, [c_f64p, C.c_int32, c_vp, c_vp]),
     "sfm_chol_solve_profiled": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_i32p, c_vp, C.c_size_t, c_vp,
                                           c_vp]),

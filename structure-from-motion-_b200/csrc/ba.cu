@@ -41,6 +41,11 @@ namespace sfm {
 
 int chol_solve_launch(double *A, size_t ld, int npad, double *d_Linv, double *d_x, int *d_fail,
                       cudaStream_t st, unsigned long long *d_prof);
+// K11s (chol_dag.cu): structure-aware factorisation, planned once per problem
+struct CholDagPlan;
+CholDagPlan *chol_dag_create(const uint8_t *h_pattern, int nb, int order_mode, cudaStream_t st, int *rc);
+int chol_dag_launch(CholDagPlan *p, const double *A, size_t ld, int npad, double *d_x, int *d_fail, cudaStream_t st);
+void chol_dag_destroy(CholDagPlan *p, cudaStream_t st);
 constexpr int BA_NB = 48;                 // == CH_NB in chol.cu
 constexpr int BA_CHUNK = 2048;            // observations per camera-pass CTA
 constexpr int K9P_WARP_SCRATCH = 9 * 33 + 18;   // doubles of shared memory per warp of K9p (T[9][33] + 34 ints, padded)
@@ -1228,6 +1233,18 @@ __global__ void ba_blk_mark_kernel(const uint32_t *__restrict__ keys, size_t n_e
     flag[hi * (hi + 1) / 2 + lo] = 1.0;                              // same value from every writer
 }
 
+// 48 x 48 block pattern of S (lower triangle, nb x nb doubles so that it can be sum-all-reduced) from the pair list
+__global__ void ba_blk48_mark_kernel(const uint32_t *__restrict__ keys, size_t n_entries, int nc, int nb,
+                                     double *__restrict__ pat) {
+    const size_t d = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d < (size_t)nb) pat[d * nb + d] = 1.0;
+    if (d >= n_entries) return;
+    const uint32_t k = keys[d];
+    if (k == SG_DEAD) return;
+    const uint32_t hi = k / (uint32_t)nc, lo = k - hi * (uint32_t)nc;
+    pat[(size_t)(6 * hi / BA_NB) * nb + 6 * lo / BA_NB] = 1.0;
+}
+
 __global__ void ba_blk_flag_kernel(const double *__restrict__ flag, size_t T, int *__restrict__ f) {
     const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t <= T) f[t] = (t < T && flag[t] != 0.0) ? 1 : 0;           // f[T] = 0: the scan leaves the total there
@@ -1808,6 +1825,8 @@ struct PlanKey {
     uint2 *pair_vals;
     size_t npairs;
     int pair_seg;
+    CholDagPlan *dag;         // K11s plan (null: not planned yet, or the dense kernel serves this problem)
+    int dag_tried;
 };
 static std::mutex g_plan_mu;
 static std::vector<PlanKey> g_plans;
@@ -1837,11 +1856,13 @@ static int ba_acquire_index(BAPlan &pl, bool reuse, const void *d_ws, const doub
     if ((rc = ba_build_pairs(pl, d_cam_idx, st, &pkeys, &pvals, &npairs, &pseg)) != SFM_OK) return rc;
     pl.pair_keys = pkeys; pl.pair_vals = pvals; pl.npairs = npairs; pl.pair_seg = pseg;
     std::lock_guard<std::mutex> g(g_plan_mu);
-    PlanKey pk{d_ws, d_cam_idx, n_cams, n_pts, n_obs, pl.nchunks, pl.max_track, pl.has_dup, pkeys, pvals, npairs, pseg};
+    PlanKey pk{d_ws, d_cam_idx, n_cams, n_pts, n_obs, pl.nchunks, pl.max_track, pl.has_dup, pkeys, pvals, npairs, pseg,
+               nullptr, 0};
     auto release = [st](PlanKey &q) {           // stream-ordered: kernels already queued on st still see the arrays
         if (q.pair_keys) cudaFreeAsync(q.pair_keys, st);
         if (q.pair_vals) cudaFreeAsync(q.pair_vals, st);
-        q.pair_keys = nullptr; q.pair_vals = nullptr; q.npairs = 0;
+        if (q.dag) chol_dag_destroy(q.dag, st);
+        q.pair_keys = nullptr; q.pair_vals = nullptr; q.npairs = 0; q.dag = nullptr; q.dag_tried = 0;
     };
     bool found = false;
     for (PlanKey &q : g_plans)
@@ -1860,10 +1881,79 @@ extern "C" int sfm_ba_release_cache(uint64_t *bytes, void *stream) {
     for (PlanKey &q : g_plans) {
         if (q.pair_keys) { SFM_CUDA_TRY(cudaFreeAsync(q.pair_keys, st)); total += sizeof(uint32_t) * (uint64_t)q.npairs; }
         if (q.pair_vals) { SFM_CUDA_TRY(cudaFreeAsync(q.pair_vals, st)); total += sizeof(uint2) * (uint64_t)q.npairs; }
-        q.pair_keys = nullptr; q.pair_vals = nullptr; q.npairs = 0;
+        if (q.dag) chol_dag_destroy(q.dag, st);
+        q.pair_keys = nullptr; q.pair_vals = nullptr; q.npairs = 0; q.dag = nullptr;
     }
     g_plans.clear();                    // index structures in the workspaces are rebuilt on the next solve
     if (bytes) *bytes = total;
+    return SFM_OK;
+}
+
+namespace sfm {
+int comm_allreduce_sum_f64(void *comm, double *buf, size_t count, cudaStream_t st);
+int comm_allreduce_max_u64(void *comm, unsigned long long *buf, size_t count, cudaStream_t st);
+}
+
+// K11s plan of this problem (once per index structure; cached with the pair list). The 48 x 48 block pattern of
+// S comes from the K10g pair list (dense when the problem is too small for one); with several GPUs every rank
+// needs the pattern of the SUMMED system, so the marks are all-reduced (a collective: every rank calls this).
+// *out stays null when the dense kernel is to be used (SFM_CHOL_DAG=0, or the task graph would be too large).
+static int ba_acquire_dag(const BAPlan &pl, const void *d_ws, void *comm, cudaStream_t st, CholDagPlan **out) {
+    *out = nullptr;
+    static int mode = -1, min_nb = 0;                 // development switches
+    if (mode < 0) {
+        const char *e = getenv("SFM_CHOL_DAG");       // 0 = dense kernel, 1 = auto order (default), 2 = natural, 3 = nested dissection
+        mode = e ? atoi(e) : 1;
+        const char *m = getenv("SFM_CHOL_DAG_MIN_NB");
+        min_nb = m ? atoi(m) : 0;
+    }
+    const int nb = pl.npad / BA_NB;
+    if (mode <= 0 || nb < min_nb) return SFM_OK;
+    {
+        std::lock_guard<std::mutex> g(g_plan_mu);
+        for (const PlanKey &pk : g_plans)
+            if (pk.ws == d_ws && pk.nc == pl.nc && pk.np == pl.np && pk.nobs == pl.nobs && pk.dag_tried) {
+                *out = pk.dag;
+                return SFM_OK;
+            }
+    }
+    keep_async_pool_cached();
+    double *pat = nullptr;
+    const size_t cells = (size_t)nb * nb;
+    SFM_CUDA_TRY(cudaMallocAsync(&pat, sizeof(double) * cells, st));
+    std::vector<double> hp(cells, 1.0);
+    if (pl.npairs) {
+        SFM_CUDA_TRY(cudaMemsetAsync(pat, 0, sizeof(double) * cells, st));
+        const size_t ne = std::max(pl.npairs, (size_t)nb);
+        ba_blk48_mark_kernel<<<(unsigned)((ne + 255) / 256), 256, 0, st>>>(pl.pair_keys, pl.npairs, pl.nc, nb, pat);
+        SFM_LAUNCH_CHECK();
+    } else {
+        SFM_CUDA_TRY(cudaMemcpyAsync(pat, hp.data(), sizeof(double) * cells, cudaMemcpyHostToDevice, st));
+    }
+    int rc;
+    if (comm && (rc = comm_allreduce_sum_f64(comm, pat, cells, st)) != SFM_OK) return rc;
+    SFM_CUDA_TRY(cudaMemcpyAsync(hp.data(), pat, sizeof(double) * cells, cudaMemcpyDeviceToHost, st));
+    SFM_CUDA_TRY(cudaStreamSynchronize(st));
+    SFM_CUDA_TRY(cudaFreeAsync(pat, st));
+    std::vector<uint8_t> hb(cells);
+    for (size_t e = 0; e < cells; ++e) hb[e] = hp[e] != 0.0;
+    rc = SFM_OK;
+    CholDagPlan *dag = chol_dag_create(hb.data(), nb, mode == 2 ? 1 : mode == 3 ? 2 : 0, st, &rc);
+    if (rc != SFM_OK) return rc;
+    std::lock_guard<std::mutex> g(g_plan_mu);
+    bool stored = false;
+    for (PlanKey &pk : g_plans)
+        if (pk.ws == d_ws && pk.nc == pl.nc && pk.np == pl.np && pk.nobs == pl.nobs) {
+            if (pk.dag) chol_dag_destroy(pk.dag, st);
+            pk.dag = dag;
+            pk.dag_tried = 1;
+            stored = true;
+        }
+    if (!stored && dag) {                      // no cache entry to own it (cannot happen after ba_acquire_index)
+        chol_dag_destroy(dag, st);
+        dag = nullptr;
+    }
+    *out = dag;
     return SFM_OK;
 }
 
@@ -1910,11 +2000,6 @@ extern "C" int sfm_ba_residuals(const double *d_cam, const double *d_pts, const 
     return SFM_OK;
 }
 
-namespace sfm {
-int comm_allreduce_sum_f64(void *comm, double *buf, size_t count, cudaStream_t st);
-int comm_allreduce_max_u64(void *comm, unsigned long long *buf, size_t count, cudaStream_t st);
-}
-
 // The LM driver. comm == nullptr: single GPU. Otherwise this rank holds a contiguous range of the
 // points (with all of their observations, local point indices) and ALL cameras; U/g_c/cost are
 // all-reduced per linearisation, S/g_red and six scalars per trial step, and every rank runs the
@@ -1938,6 +2023,8 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
 
     if ((rc = ba_acquire_index(pl, o.reuse_index != 0, d_ws, obs, d_cam_idx, d_pt_idx, n_cams, n_pts, n_obs, st)) != SFM_OK) return rc;
     const int nc = pl.nc, np = pl.np, nobs = pl.nobs, n = 6 * nc;
+    CholDagPlan *dag = nullptr;
+    if ((rc = ba_acquire_dag(pl, d_ws, comm, st, &dag)) != SFM_OK) return rc;
     // multi-GPU + K10g: block list of the sparse all-reduce (a collective: every rank takes this branch or none;
     // ranks whose shard is too small for K10g would break that, so the decision is all-reduced first)
     uint32_t *blk_list = nullptr;
@@ -2154,7 +2241,9 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
             if (cprof && (cudaMalloc(&d_cprof, 8 * sizeof(unsigned long long)) != cudaSuccess ||
                           cudaMemset(d_cprof, 0, 8 * sizeof(unsigned long long)) != cudaSuccess)) cprof = 0;
         }
-        if ((rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st, cprof ? d_cprof : nullptr)) != SFM_OK) return rc;
+        if (dag) rc = chol_dag_launch(dag, pl.S, pl.ld, pl.npad, pl.dc, pl.flags + 2, st);
+        else rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st, cprof ? d_cprof : nullptr);
+        if (rc != SFM_OK) return rc;
         if (cprof) {
             unsigned long long hp[8];
             cudaStreamSynchronize(st);
