@@ -253,7 +253,8 @@ int sfm_chol_solve(const double *d_S, const double *d_g, int32_t n, double *d_x,
  *   order_mode 0 = pick the order with the shortest simulated schedule, 1 = natural, 2 = nested dissection
  *   repeats    the factor + solve is launched this many times (timing); results of the last launch
  *   d_fail[0]  1 = a pivot was not positive, 2 = an internal wait timed out (scheduling bug)
- *   h_info[4]  optional HOST out: {order kind, elimination-tree height, off-diagonal L blocks, simulated us}
+ *   h_info[6]  optional HOST out: {order kind, elimination-tree height, off-diagonal L blocks, simulated us,
+ *              measured ms per launch (CUDA events over the repeats), partial-sum tasks}
  * Workspace as sfm_chol_solve. Replaces what MINPACK's dense QR does behind BundleAdjustment.py:205-212. */
 int sfm_chol_solve_structured(const double *d_S, const double *d_g, int32_t n, int32_t order_mode,
                               int32_t repeats, double *d_x, int32_t *d_fail, void *d_ws, size_t ws_bytes,

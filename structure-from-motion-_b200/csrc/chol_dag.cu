@@ -22,6 +22,7 @@
 #include "chol_blocks.cuh"
 #include "chol_plan.h"
 #include <cooperative_groups.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
@@ -36,11 +37,15 @@ constexpr int DG_VIEW = CH_NB * CH_LDS;                    // doubles per shared
 constexpr int DG_BLK = CH_NB * CH_NB;                      // doubles per compact block
 constexpr unsigned long long DG_TIMEOUT_NS = 400ull * 1000 * 1000;   // a wait this long is a scheduling bug
 
+constexpr int DG_VIEWS = 11;                               // shared-memory block views of a backward task (220 of 227 KB)
+
 struct DagSmem {
     CholSmem c;                 // eight block views + the diagonal factor's scratch
+    double more[(DG_VIEWS - 8) * DG_VIEW];   // views 8 .. of the backward tasks
     double v[64];               // running right-hand side of a diag task
     double yt[2][64];           // y_t of the staged product
-    double red[4 * 64];
+    double red[2 * 4 * 64];
+    double xs[DG_VIEWS * CH_NB];   // x_i of the staged blocks of a backward task
     int nready, abort, pre;
 };
 
@@ -50,6 +55,7 @@ struct DagDev {
     const DagEntry *entries;
     const int32_t *fwd_ptr, *fwd_list, *bwd_ptr, *bwd_list, *perm;
     double *Lc, *Linv, *y, *xe, *pvec;
+    unsigned long long *trace;  // optional [n_tasks][4] ns: task start, operands complete, end, SM id (SFM_CHOL_DAG_TRACE)
     unsigned *flags;            // [nblk] off-diagonal + scratch blocks | [nb] diagonal | [nb] x | [1] abort
 };
 
@@ -118,10 +124,12 @@ chol_dag_kernel(const double *__restrict__ S, size_t ld, DagDev pv, unsigned epo
 
     // ------------------------------------------------------------------ forward: factor + y
     for (int q = pv.fwd_ptr[cta]; q < pv.fwd_ptr[cta + 1] && !sm.abort; ++q) {
-        const DagTask t = pv.tasks[pv.fwd_list[q]];
+        const int task_id = pv.fwd_list[q];
+        const DagTask t = pv.tasks[task_id];
         const int n = t.end - t.beg;
         const DagEntry *ent = pv.entries + t.beg;
         const bool diag = t.type == DAG_DIAG;
+        if (pv.trace && tid == 0) pv.trace[4 * (size_t)task_id] = globaltimer_ns();
         const bool rhs_part = diag || (t.type == DAG_PART && t.i == 1);     // carries a right-hand-side piece
         __syncthreads();                                    // views of the previous task are dead
         // which leading products have their operands already? (one flag pair per thread, checked once)
@@ -220,6 +228,7 @@ chol_dag_kernel(const double *__restrict__ S, size_t ld, DagDev pv, unsigned epo
             }
         }
         if (!ok) break;
+        if (pv.trace && tid == 0) pv.trace[4 * (size_t)task_id + 1] = globaltimer_ns();
         if (diag) {
             if (vrow >= 0 && vrow < CH_NB) sm.v[vrow] = vr;
             __syncthreads();
@@ -274,6 +283,10 @@ chol_dag_kernel(const double *__restrict__ S, size_t ld, DagDev pv, unsigned epo
                 st_release_u32(f_off + t.dst, epoch);
             }
         }
+        if (pv.trace && tid == 0) {
+            pv.trace[4 * (size_t)task_id + 2] = globaltimer_ns();
+            pv.trace[4 * (size_t)task_id + 3] = (unsigned long long)cta;
+        }
     }
     cp_async_wait<0>();
     grid.sync();
@@ -283,33 +296,58 @@ chol_dag_kernel(const double *__restrict__ S, size_t ld, DagDev pv, unsigned epo
     }
 
     // ------------------------------------------------------------------ backward: L^T x = y
+    // x_j = L_jj^-T (y_j - sum_i L_ij^T x_i). L is final, so the blocks of a column stream into the eight
+    // shared-memory views BEFORE the task waits for the x_i it needs; after the wait only the x_i themselves
+    // (one L2 round trip) and shared-memory mat-vecs remain on the chain root -> leaves.
     const int c = tid & 63, part = tid >> 6;
+    constexpr int BK = DG_VIEWS;                              // blocks staged per batch
+    auto bview = [&](int e) { return e < 8 ? V0 + e * DG_VIEW : sm.more + (e - 8) * DG_VIEW; };
     for (int q = pv.bwd_ptr[cta]; q < pv.bwd_ptr[cta + 1]; ++q) {
-        const DagTask t = pv.tasks[pv.bwd_list[q]];
+        const int task_id = pv.bwd_list[q];
+        const DagTask t = pv.tasks[task_id];
         const int n = t.end - t.beg;
         const DagEntry *ent = pv.entries + t.beg;
-        // everything that does not depend on x is requested before the wait
+        if (pv.trace && tid == 0) pv.trace[4 * (size_t)task_id] = globaltimer_ns();
         double li[12];
         const double *Li = pv.Linv + (size_t)t.j * DG_BLK;
 #pragma unroll
         for (int r = 0; r < 12; ++r) li[r] = (c < CH_NB) ? __ldcg(&Li[(part * 12 + r) * CH_NB + c]) : 0.0;
         double w = (part == 0 && c < CH_NB) ? __ldcg(&pv.y[(size_t)t.j * CH_NB + c]) : 0.0;
-        __syncthreads();
-        for (int e = tid; e < n; e += CH_THREADS)
-            if (!spin_flag(f_x + ent[e].b, epoch, abort_w)) sm.abort = 1;
-        __syncthreads();
-        if (sm.abort) break;
-#pragma unroll 4
-        for (int e = 0; e < n; ++e) {
-            const double *L = pv.Lc + (size_t)ent[e].a * DG_BLK;
-            const double *xi = pv.xe + (size_t)ent[e].b * CH_NB;
+        // entries ascend in row position: entry 0 is the parent, whose x arrives last. Batches (columns longer
+        // than the views) are taken from the far end, each waiting only for its own x_i.
+        for (int e0 = ((n - 1) / BK) * BK; e0 >= 0 && n > 0; e0 -= BK) {
+            const int ne = min(BK, n - e0);
+            __syncthreads();                                  // views and xs of the previous batch / task are dead
+            for (int e = 0; e < ne; ++e) issue_block(bview(e), pv.Lc + (size_t)ent[e0 + e].a * DG_BLK);
+            cp_async_commit();
+            for (int e = tid; e < ne; e += CH_THREADS)
+                if (!spin_flag(f_x + ent[e0 + e].b, epoch, abort_w)) sm.abort = 1;
+            __syncthreads();
+            if (sm.abort) break;
+            if (pv.trace && tid == 0 && e0 == 0) pv.trace[4 * (size_t)task_id + 1] = globaltimer_ns();
+            for (int k = tid; k < ne * CH_NB; k += CH_THREADS) {
+                const int e = k / CH_NB, r = k - e * CH_NB;
+                sm.xs[k] = __ldcg(&pv.xe[(size_t)ent[e0 + e].b * CH_NB + r]);
+            }
+            cp_async_wait<0>();
+            __syncthreads();
             if (c < CH_NB) {
-                double a = 0.0;
+                double a0 = 0.0, a1 = 0.0;
+                for (int e = 0; e < ne; ++e) {
+                    const double *L = bview(e) + (part * 12) * CH_LDS + c;
+                    const double *xi = sm.xs + e * CH_NB + part * 12;
 #pragma unroll
-                for (int r = 0; r < 12; ++r) a = fma(__ldcg(&L[(part * 12 + r) * CH_NB + c]), __ldcg(&xi[part * 12 + r]), a);
-                w -= a;
+                    for (int r = 0; r < 12; r += 2) {
+                        a0 = fma(L[r * CH_LDS], xi[r], a0);
+                        a1 = fma(L[(r + 1) * CH_LDS], xi[r + 1], a1);
+                    }
+                }
+                w -= a0 + a1;
             }
         }
+        if (sm.abort) break;
+        if (pv.trace && tid == 0 && n == 0) pv.trace[4 * (size_t)task_id + 1] = globaltimer_ns();
+        __syncthreads();
         sm.red[part * 64 + c] = w;
         __syncthreads();
         if (tid < CH_NB) sm.v[tid] = sm.red[tid] + sm.red[64 + tid] + sm.red[128 + tid] + sm.red[192 + tid];
@@ -319,12 +357,11 @@ chol_dag_kernel(const double *__restrict__ S, size_t ld, DagDev pv, unsigned epo
 #pragma unroll
             for (int r = 0; r < 12; ++r)
                 if (part * 12 + r >= c) a = fma(li[r], sm.v[part * 12 + r], a);
-            __syncthreads();
-            sm.red[part * 64 + c] = a;
+            sm.red[256 + part * 64 + c] = a;
         }
         __syncthreads();
         if (tid < CH_NB) {
-            const double x = sm.red[tid] + sm.red[64 + tid] + sm.red[128 + tid] + sm.red[192 + tid];
+            const double x = sm.red[256 + tid] + sm.red[256 + 64 + tid] + sm.red[256 + 128 + tid] + sm.red[256 + 192 + tid];
             pv.xe[(size_t)t.j * CH_NB + tid] = x;
             x_out[(size_t)t.src_r * CH_NB + tid] = x;
         }
@@ -332,6 +369,10 @@ chol_dag_kernel(const double *__restrict__ S, size_t ld, DagDev pv, unsigned epo
         if (tid == 0) {
             __threadfence();
             st_release_u32(f_x + t.j, epoch);
+            if (pv.trace) {
+                pv.trace[4 * (size_t)task_id + 2] = globaltimer_ns();
+                pv.trace[4 * (size_t)task_id + 3] = (unsigned long long)cta;
+            }
         }
     }
     if (sm.abort && tid == 0) *fail_flag = 2;
@@ -407,6 +448,8 @@ CholDagPlan *chol_dag_create(const uint8_t *h_pattern, int nb, int order_mode, c
     const size_t o_y = take(sizeof(double) * (size_t)nb * CH_NB);
     const size_t o_xe = take(sizeof(double) * (size_t)nb * CH_NB);
     const size_t o_pvec = take(sizeof(double) * std::max<size_t>((size_t)h.n_part, 1) * CH_NB);
+    const char *trace_path = getenv("SFM_CHOL_DAG_TRACE");
+    const size_t o_trace = take(trace_path ? sizeof(unsigned long long) * 4 * h.tasks.size() : 0);
     const size_t o_Lc = take(sizeof(double) * std::max<size_t>(nblk, 1) * DG_BLK);
     p->blob_bytes = off;
     if (cudaMallocAsync(&p->blob, off, st) != cudaSuccess) {
@@ -449,6 +492,7 @@ CholDagPlan *chol_dag_create(const uint8_t *h_pattern, int nb, int order_mode, c
     d.y = reinterpret_cast<double *>(base + o_y);
     d.xe = reinterpret_cast<double *>(base + o_xe);
     d.pvec = reinterpret_cast<double *>(base + o_pvec);
+    d.trace = trace_path ? reinterpret_cast<unsigned long long *>(base + o_trace) : nullptr;
     d.Lc = reinterpret_cast<double *>(base + o_Lc);
     return p;
 }
@@ -473,6 +517,24 @@ int chol_dag_launch(CholDagPlan *p, const double *A, size_t ld, int npad, double
 }
 
 const CholDagHost &chol_dag_host(const CholDagPlan *p) { return p->h; }
+
+// SFM_CHOL_DAG_TRACE=<file>: per-task timestamps of the last launch, written as
+// int64 n_tasks | tasks [n_tasks][12] int32 | trace [n_tasks][4] uint64 (diagnostic, tools/chol_dag_trace.py)
+static void chol_dag_dump_trace(const CholDagPlan *p, cudaStream_t st) {
+    const char *path = getenv("SFM_CHOL_DAG_TRACE");
+    if (!path || !p->d.trace) return;
+    const size_t nt = p->h.tasks.size();
+    std::vector<unsigned long long> tr(4 * nt);
+    if (cudaStreamSynchronize(st) != cudaSuccess ||
+        cudaMemcpy(tr.data(), p->d.trace, sizeof(unsigned long long) * 4 * nt, cudaMemcpyDeviceToHost) != cudaSuccess) return;
+    FILE *f = fopen(path, "wb");
+    if (!f) return;
+    const int64_t n64 = (int64_t)nt;
+    fwrite(&n64, sizeof(n64), 1, f);
+    fwrite(p->h.tasks.data(), sizeof(DagTask), nt, f);
+    fwrite(tr.data(), sizeof(unsigned long long), 4 * nt, f);
+    fclose(f);
+}
 
 // dense S [n,n] + g [n] -> the padded layout (identity on the padding diagonal, g in row npad)
 __global__ void chol_dag_pack_kernel(const double *__restrict__ S, const double *__restrict__ g, int n, int npad,
@@ -521,7 +583,7 @@ extern "C" int sfm_chol_plan_export(const uint8_t *h_pattern, int32_t nb, int32_
 // ---- standalone entry (tests, tools): dense SPD S [n,n] + g [n] -> x, through the structure-aware kernel.
 // The block pattern is read off the numeric zeros of S. Workspace: sfm_chol_solve_workspace_bytes(n).
 // Host-synchronous (plans on the host). order_mode: 0 auto, 1 natural, 2 nested dissection.
-// h_info[4] (optional) = {order_kind, tree depth, nnzL blocks, simulated us}.
+// h_info[6] (optional) = {order_kind, tree depth, nnzL blocks, simulated us, measured ms per launch (CUDA events), partial tasks}.
 extern "C" int sfm_chol_solve_structured(const double *d_S, const double *d_g, int32_t n, int32_t order_mode,
                                          int32_t repeats, double *d_x, int32_t *d_fail, void *d_ws, size_t ws_bytes,
                                          double *h_info, void *stream) {
@@ -546,15 +608,26 @@ extern "C" int sfm_chol_solve_structured(const double *d_S, const double *d_g, i
     if (!plan) return rc != SFM_OK ? rc : SFM_E_NOT_CONVERGED;
     chol_dag_pack_kernel<<<sm_count() * 4, 256, 0, st>>>(d_S, d_g, n, npad, ld, A);
     count_launch();
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float ms = 0.f;
+    if (h_info) { cudaEventCreate(&ev0); cudaEventCreate(&ev1); cudaEventRecord(ev0, st); }
     for (int r = 0; r < repeats && rc == SFM_OK; ++r) rc = chol_dag_launch(plan, A, ld, npad, x, flag, st);
+    if (h_info) {
+        cudaEventRecord(ev1, st);
+        cudaEventSynchronize(ev1);
+        cudaEventElapsedTime(&ms, ev0, ev1);
+        cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    }
     if (rc == SFM_OK) {
         SFM_CUDA_TRY(cudaMemcpyAsync(d_x, x, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st));
         SFM_CUDA_TRY(cudaMemcpyAsync(d_fail, flag, sizeof(int), cudaMemcpyDeviceToDevice, st));
         SFM_CUDA_TRY(cudaStreamSynchronize(st));
     }
+    chol_dag_dump_trace(plan, st);
     if (h_info) {
         const CholDagHost &h = chol_dag_host(plan);
         h_info[0] = h.order_kind; h_info[1] = h.depth; h_info[2] = h.nnzL; h_info[3] = h.sim_fwd_us + h.sim_bwd_us;
+        h_info[4] = (double)ms / repeats; h_info[5] = h.n_part;
     }
     chol_dag_destroy(plan, st);
     return rc;

@@ -178,8 +178,8 @@ void symbolic(const uint8_t *pattern, int nb, const std::vector<int32_t> &perm, 
 }
 
 // simulated costs [us] of the executor's steps on B200 (rough; they only rank schedules)
-constexpr double C_LOAD = 0.8, C_PROD = 1.1, C_FACTOR = 8.5, C_TRSM = 2.2, C_LAT = 0.8;
-constexpr double C_BACK = 1.6, C_BACK_ENT = 0.2, C_ADD = 0.4, C_STORE = 0.8;
+constexpr double C_LOAD = 0.8, C_PROD = 1.3, C_FACTOR = 8.8, C_TRSM = 3.5, C_LAT = 0.9;   // calibrated on a task trace of the C5 system
+constexpr double C_BACK = 3.4, C_ADD = 0.5, C_STORE = 1.0;
 
 struct Built {
     std::vector<DagTask> tasks;
@@ -389,65 +389,25 @@ Sched schedule_forward(const Built &b, int G) {
     return s;
 }
 
-// backward tasks: x_j needs x_i of every row i of column j
+// backward tasks: x_j needs x_i of every row i of column j. A task streams the blocks of its column into shared
+// memory BEFORE it waits for those x_i, so it should be started long before its turn: the columns are sorted by
+// their level below the roots of the elimination tree (a topological order) and dealt round-robin -- with
+// nb <= G every task has a CTA of its own and the chain pays one flag latency + one small mat-vec per level.
 Sched schedule_backward(const Built &b, const Symbolic &sy, int G) {
     const int nb = sy.nb, base = b.n_fwd;
     auto tid = [&](int j) { return base + (nb - 1 - j); };
-    std::vector<double> fin(nb, -1.0), prio(nb, 0.0);
-    // priority: longest chain below (towards the leaves): users of x_i are the columns j with i in struct(j)
-    for (int j = 0; j < nb; ++j) {
-        // processed ascending: prio[j] known before its rows (which come later)? no: x_i (i > j) feeds x_j,
-        // so the chain runs from high positions to low ones; accumulate from low to high
-        const double dur = C_BACK + C_BACK_ENT * (sy.colptr[j + 1] - sy.colptr[j]) + C_LAT;
-        prio[j] += dur;
-        for (int p = sy.colptr[j]; p < sy.colptr[j + 1]; ++p) prio[sy.rowidx[p]] = std::max(prio[sy.rowidx[p]], prio[j]);
+    std::vector<int> lev(nb, 0), order(nb);
+    int maxlev = 0;
+    for (int j = nb - 1; j >= 0; --j) {
+        for (int p = sy.colptr[j]; p < sy.colptr[j + 1]; ++p) lev[j] = std::max(lev[j], lev[sy.rowidx[p]] + 1);
+        maxlev = std::max(maxlev, lev[j]);
     }
-    std::vector<int> waiting(nb, 0);
-    std::vector<std::vector<int>> users(nb);
-    for (int j = 0; j < nb; ++j) {
-        waiting[j] = sy.colptr[j + 1] - sy.colptr[j];
-        for (int p = sy.colptr[j]; p < sy.colptr[j + 1]; ++p) users[sy.rowidx[p]].push_back(j);
-    }
-    typedef std::pair<double, int> PD;
-    std::priority_queue<PD, std::vector<PD>, std::greater<PD>> pending, ctas;
-    std::priority_queue<PD> ready;
-    for (int j = 0; j < nb; ++j)
-        if (!waiting[j]) pending.push(PD(0.0, j));
-    for (int c = 0; c < G; ++c) ctas.push(PD(0.0, c));
+    for (int j = 0; j < nb; ++j) order[j] = j;
+    std::sort(order.begin(), order.end(), [&](int x, int y) { return lev[x] != lev[y] ? lev[x] < lev[y] : x > y; });
     std::vector<std::vector<int32_t>> lists(G);
-    int assigned = 0;
-    double makespan = 0.0;
-    while (assigned < nb) {
-        PD c = ctas.top();
-        ctas.pop();
-        const double T = c.first;
-        while (!pending.empty() && pending.top().first <= T) {
-            ready.push(PD(prio[pending.top().second], pending.top().second));
-            pending.pop();
-        }
-        if (ready.empty()) {
-            if (pending.empty()) break;
-            ctas.push(PD(pending.top().first, c.second));
-            continue;
-        }
-        const int j = ready.top().second;
-        ready.pop();
-        double rdy = T;
-        for (int p = sy.colptr[j]; p < sy.colptr[j + 1]; ++p) rdy = std::max(rdy, fin[sy.rowidx[p]] + C_LAT);
-        fin[j] = rdy + C_BACK + C_BACK_ENT * (sy.colptr[j + 1] - sy.colptr[j]);
-        makespan = std::max(makespan, fin[j]);
-        lists[c.second].push_back(tid(j));
-        ++assigned;
-        ctas.push(PD(fin[j], c.second));
-        for (int u : users[j])
-            if (--waiting[u] == 0) {
-                double el = 0.0;
-                for (int p = sy.colptr[u]; p < sy.colptr[u + 1]; ++p) el = std::max(el, fin[sy.rowidx[p]]);
-                pending.push(PD(el, u));
-            }
-    }
+    for (int k = 0; k < nb; ++k) lists[k % G].push_back(tid(order[k]));
     Sched s;
-    s.makespan = assigned == nb ? makespan : -1.0;
+    s.makespan = (maxlev + 1) * (C_BACK + C_LAT) * std::max(1.0, (double)nb / (4.0 * G));
     s.ptr.assign(G + 1, 0);
     for (int c = 0; c < G; ++c) {
         s.ptr[c] = (int32_t)s.list.size();

@@ -106,7 +106,7 @@ def test_chol_structured_matches_lapack(cuda_device, kind, order_mode):
     d_x = device.empty((n,), torch.float64)
     d_fail = device.empty((1,), torch.int32)
     d_S, d_g = device.to_device(np.tril(S)), device.to_device(g)
-    info = np.zeros(4)
+    info = np.zeros(6)
     _lib.check(lib.sfm_chol_solve_structured(device.ptr(d_S), device.ptr(d_g), n, order_mode, 3, device.ptr(d_x),
                                              device.ptr(d_fail), device.ptr(ws), nbytes, info.ctypes.data,
                                              device.stream()), "sfm_chol_solve_structured")
