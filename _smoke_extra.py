@@ -13,7 +13,8 @@ import numpy as np
 def run() -> str:
     from oracle import ba_oracle as bo
     from oracle import sfm_oracle as so
-    from . import _lib, bundle, homography, refine, scenes, two_view
+    from sfm_b200 import _lib, bundle, homography, refine, two_view
+    from oracle import scenes
 
     before = _lib.launch_count()
     # N1 + K5: linear then non-linear triangulation

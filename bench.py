@@ -128,7 +128,8 @@ class ClockSampler:
 
 
 def make_inputs(n_hyp_total):
-    from sfm_b200 import sampler, scenes
+    from sfm_b200 import sampler
+    from oracle import scenes
     sc = scenes.two_view(n=N_PTS, seed=DATA_SEED)
     random.seed(RNG_SEED)
     samples = sampler.sample_stream(N_PTS, 8, n_hyp_total)

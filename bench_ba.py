@@ -21,7 +21,7 @@ C5 = dict(n_cams=1000, n_pts=500_000, obs_per_pt=8, seed=20260106, layout="ring"
 
 def _scene(cfg):
     from scipy.spatial.transform import Rotation
-    from sfm_b200 import scenes
+    from oracle import scenes
     sc = scenes.ba_scene(**cfg)
     cams0 = np.hstack([Rotation.from_matrix(sc["R0"]).as_rotvec(),
                        -np.einsum("nij,nj->ni", sc["R0"], sc["C0"])])
@@ -93,7 +93,7 @@ def cpu_baseline(seconds_budget=20.0):
     finish; the reference cannot run configs[2] at all."""
     from scipy.spatial.transform import Rotation
     from oracle import ba_oracle as bo
-    from sfm_b200 import scenes
+    from oracle import scenes
     nc, npts, k = 12, 300, 6
     sc = scenes.ba_scene(n_cams=nc, n_pts=npts, obs_per_pt=k, seed=9)
     cams0 = np.hstack([Rotation.from_matrix(sc["R0"]).as_rotvec(), -np.einsum("nij,nj->ni", sc["R0"], sc["C0"])])

@@ -37,7 +37,7 @@ def _timed(fn, flush, reps=5):
 def cpu_baseline(sc, P_pts=3000, n_pnp=20):
     """The oracle port on one core: P_pts points of the same scene, n_pnp registrations."""
     from oracle import sfm_oracle as so
-    from sfm_b200 import scenes
+    from oracle import scenes
     idx = np.arange(P_pts)
     t0 = time.perf_counter()
     X0 = so.linear_triangulation(sc["K"], sc["C1"], sc["R1"], sc["C2"], sc["R2"], sc["x1"][idx], sc["x2"][idx])
@@ -59,7 +59,8 @@ def cpu_baseline(sc, P_pts=3000, n_pnp=20):
 def run(flush=None, with_cpu=True):
     import torch
     from scipy.spatial.transform import Rotation
-    from sfm_b200 import device, refine, scenes
+    from sfm_b200 import device, refine
+    from oracle import scenes
     sc = scenes.two_view(n=N_PTS, outlier_frac=0.0, noise=0.5, seed=20260104)
     P1 = refine.projection_matrix(sc["K"], sc["C1"], sc["R1"])
     P2 = refine.projection_matrix(sc["K"], sc["C2"], sc["R2"])

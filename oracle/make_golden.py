@@ -23,7 +23,7 @@ OUT = os.path.join(ROOT, "tests", "golden")
 sys.path.insert(0, ROOT)
 sys.path.insert(0, REF)  # reference modules import each other by bare name
 
-from sfm_b200 import scenes  # noqa: E402  (data generators only)
+from oracle import scenes  # noqa: E402  (data generators only)
 
 # matplotlib is absent here; Utils.py imports it at module level (Utils.py:4-5). Stub it.
 for name in ("matplotlib", "matplotlib.pyplot", "mpl_toolkits", "mpl_toolkits.mplot3d"):

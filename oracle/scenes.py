@@ -1,4 +1,7 @@
-"""Synthetic scenes of the shapes BASELINE.json names. Data generation
+"""TEST AND BENCH INFRASTRUCTURE (lives under oracle/ so that no product module and not the reference arm of
+bench.py has to import the product package for its inputs).
+
+Synthetic scenes of the shapes BASELINE.json names. Data generation
 only (numpy); shared by tests/ and bench.py so that both sides of every comparison see the
 same seeded inputs."""
 from __future__ import annotations

@@ -18,7 +18,8 @@ def main():
     import torch
     import torch.distributed as dist
     from scipy.spatial.transform import Rotation
-    from sfm_b200 import bundle, bundle_mgpu, device, ransac, sampler, scenes
+    from sfm_b200 import bundle, bundle_mgpu, device, ransac, sampler
+    from oracle import scenes
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))

@@ -175,7 +175,8 @@ def test_perform_bundle_adjustment_matches_reference(cuda_device, schur_path, ta
 
 @pytest.mark.parametrize("nc,npts,k,seed", [(8, 150, 5, 7), (12, 300, 6, 9), (20, 800, 7, 11)])
 def test_ba_sparse_matches_oracle_lm(cuda_device, schur_path, nc, npts, k, seed):
-    from sfm_b200 import bundle, scenes
+    from sfm_b200 import bundle
+    from oracle import scenes
     sc = scenes.ba_scene(n_cams=nc, n_pts=npts, obs_per_pt=k, seed=seed)
     cams0, pts0 = _x0(sc)
     x0 = np.concatenate([cams0.reshape(-1), pts0.reshape(-1)])
@@ -193,7 +194,8 @@ def test_ba_sparse_matches_oracle_lm(cuda_device, schur_path, nc, npts, k, seed)
 def test_ba_long_tracks_and_duplicate_cameras(cuda_device, schur_path):
     """Points seen by more than 32 cameras take the global-memory Schur path; an observation list
     that names the same camera twice on one point must still match the oracle."""
-    from sfm_b200 import bundle, scenes
+    from sfm_b200 import bundle
+    from oracle import scenes
     sc = scenes.ba_scene(n_cams=40, n_pts=120, obs_per_pt=36, seed=21)
     cam_idx, pt_idx, obs = sc["cam_idx"].copy(), sc["pt_idx"].copy(), sc["obs"].copy()
     # duplicate a few observations (same camera, slightly different pixel) on short-track points
@@ -215,7 +217,8 @@ def test_ba_long_tracks_and_duplicate_cameras(cuda_device, schur_path):
 
 
 def test_ba_error_conventions(cuda_device):
-    from sfm_b200 import _lib, bundle, scenes
+    from sfm_b200 import _lib, bundle
+    from oracle import scenes
     g = {k: v for k, v in golden("ba_a.npz").items()}       # materialise once: identity checks below
     nc = len(g["R0"])
     R_set, C_set = [r for r in g["R0"]], [c for c in g["C0"]]
@@ -259,7 +262,8 @@ def test_ba_c3_scale_properties(cuda_device):
     """BASELINE config 3 (50 cameras, 20k points, 200k observations): the reference cannot run it
     (SURVEY 6), so check size-independent properties: monotone decrease to a stationary point whose
     RMSE is at the noise level, determinism, and agreement of K8 with the oracle residual."""
-    from sfm_b200 import bundle, device, scenes
+    from sfm_b200 import bundle, device
+    from oracle import scenes
     sc = scenes.ba_scene()
     cams0, pts0 = _x0(sc)
     nobs = len(sc["obs"])
@@ -287,7 +291,8 @@ def test_schur_pair_list_equals_atomic_path(cuda_device, monkeypatch):
     """K10g against K10 on one damped trial system: same parameters after a fixed number of trial steps
     (the two kernels sum the same products in different orders, so agreement is to rounding, far inside
     the 1e-6 cost tolerance), on a scene with long tracks, duplicated cameras and a camera seen once."""
-    from sfm_b200 import bundle, scenes
+    from sfm_b200 import bundle
+    from oracle import scenes
     sc = scenes.ba_scene(n_cams=30, n_pts=2500, obs_per_pt=9, seed=5)
     cam_idx, pt_idx, obs = sc["cam_idx"].copy(), sc["pt_idx"].copy(), sc["obs"].copy()
     dup = np.arange(3, len(cam_idx), 101)
@@ -314,7 +319,8 @@ def test_schur_pair_list_equals_atomic_path(cuda_device, monkeypatch):
 def test_release_cache_frees_pair_lists_and_solves_again(cuda_device, monkeypatch):
     """sfm_ba_release_cache drops the cached pair lists (reported in bytes); the next solve rebuilds them and
     returns the same result."""
-    from sfm_b200 import bundle, scenes
+    from sfm_b200 import bundle
+    from oracle import scenes
     monkeypatch.setenv("SFM_SCHUR_PAIRS_MIN", "0")
     sc = scenes.ba_scene(n_cams=10, n_pts=400, obs_per_pt=5, seed=3)
     cams0, pts0 = _x0(sc)

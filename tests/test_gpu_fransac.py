@@ -80,7 +80,7 @@ def test_fransac_p3data(cuda_device, pair):
 
 def test_fransac_c2_shape_prefix(cuda_device):
     """C2 inputs (50k correspondences, 30% outliers) with a 300-hypothesis prefix of the stream."""
-    from sfm_b200 import scenes
+    from oracle import scenes
     sc = scenes.two_view()
     random.seed(12345)
     samples = so.draw_samples(len(sc["x1"]), 8, 300)
@@ -91,7 +91,8 @@ def test_fransac_c2_shape_prefix(cuda_device):
 def test_fransac_full_size_properties(cuda_device):
     """C2 at full size (100k hypotheses): size-independent properties instead of the oracle."""
     import torch
-    from sfm_b200 import scenes, sampler, device
+    from sfm_b200 import sampler, device
+    from oracle import scenes
     ransac = _ransac()
     sc = scenes.two_view()
     random.seed(12345)
@@ -158,7 +159,8 @@ def test_fransac_stream_equals_single_call(cuda_device):
     """The chunk-pipelined host path (RNG replay overlapped with K1/K2) consumes the same draws and
     returns the same winner, F and mask as one sfm_f_ransac call; the drop-in switches to it for
     large n_max and leaves the global generator in the state the reference would."""
-    from sfm_b200 import scenes, sampler
+    from sfm_b200 import sampler
+    from oracle import scenes
     ransac = _ransac()
     sc = scenes.two_view(n=4000, seed=5)
     x1, x2 = sc["x1"], sc["x2"]
@@ -188,7 +190,8 @@ def test_certified_fp32_scoring_equals_fp64_kernel(cuda_device):
     C2 scene, on P3Data-like integer coordinates, and on non-finite / badly scaled hypotheses."""
     import ctypes as C
     import torch
-    from sfm_b200 import _lib, scenes, sampler, device
+    from sfm_b200 import _lib, sampler, device
+    from oracle import scenes
     lib = _lib.load()
     sc = scenes.two_view()
     n, h = len(sc["x1"]), 6000

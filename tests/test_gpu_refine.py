@@ -34,7 +34,8 @@ def test_nltri_golden(cuda_device):
 def test_nltri_matches_hostsim_bitwise_and_oracle_at_scale(cuda_device):
     """20k points: the CUDA kernel against the live oracle on a 400-point sample, plus
     size-independent properties on all of them (cost never increases, idempotence)."""
-    from sfm_b200 import refine, scenes
+    from sfm_b200 import refine
+    from oracle import scenes
     sc = scenes.two_view(n=20_000, outlier_frac=0.0, seed=77)
     rng = np.random.default_rng(1)
     x0 = sc["X"] + rng.normal(0, 0.05, sc["X"].shape)
@@ -71,7 +72,8 @@ def test_nlpnp_golden(cuda_device, tag):
 
 def test_nlpnp_batch_matches_single_and_oracle(cuda_device):
     from scipy.spatial.transform import Rotation
-    from sfm_b200 import refine, scenes
+    from sfm_b200 import refine
+    from oracle import scenes
     rng = np.random.default_rng(5)
     Xs, xs, Cs, Rs = [], [], [], []
     for b in range(12):

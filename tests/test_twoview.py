@@ -127,7 +127,8 @@ def test_gpu_two_view_full_size_properties(cuda_device):
     """1M correspondences: the selected configuration puts (almost) every inlier in front of both cameras,
     the other three almost none; votes equal a recount from the returned points."""
     import torch
-    from sfm_b200 import scenes, two_view, device
+    from sfm_b200 import two_view, device
+    from oracle import scenes
     sc = scenes.two_view(n=1_000_000, outlier_frac=0.0, seed=77)
     F = so.estimate_fundamental_matrix(sc["x1"][:2000], sc["x2"][:2000]) if hasattr(so, "estimate_fundamental_matrix") else None
     if F is None:

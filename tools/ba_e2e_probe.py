@@ -4,7 +4,8 @@ import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from scipy.spatial.transform import Rotation
-from sfm_b200 import bundle, scenes
+from sfm_b200 import bundle
+from oracle import scenes
 sc = scenes.ba_scene()
 cams0 = np.hstack([Rotation.from_matrix(sc["R0"]).as_rotvec(), -np.einsum("nij,nj->ni", sc["R0"], sc["C0"])])
 for i in range(8):

@@ -21,7 +21,8 @@ def main():
     a = ap.parse_args()
     import torch
     from scipy.spatial.transform import Rotation
-    from sfm_b200 import bundle, device, scenes
+    from sfm_b200 import bundle, device
+    from oracle import scenes
     t0 = time.time()
     if a.config == "c3":
         sc = scenes.ba_scene()

@@ -6,7 +6,8 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from scipy.spatial.transform import Rotation
-from sfm_b200 import device, refine, scenes
+from sfm_b200 import device, refine
+from oracle import scenes
 
 
 def timed(fn, reps=5):

@@ -4,7 +4,8 @@ with perf_counter, with and without device synchronisation after each."""
 import os, random, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
-from sfm_b200 import ransac, scenes, sampler, device, _lib
+from sfm_b200 import ransac, sampler, device, _lib
+from oracle import scenes
 
 sc = scenes.two_view()
 idx = np.arange(50000)

@@ -2,7 +2,8 @@
 import sys, time, random, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
-from sfm_b200 import ransac, scenes
+from sfm_b200 import ransac
+from oracle import scenes
 sc = scenes.two_view()
 idx = np.arange(50000)
 random.seed(1)

@@ -12,7 +12,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import torch
 
-from sfm_b200 import _lib, device, sampler, scenes
+from sfm_b200 import _lib, device, sampler
+from oracle import scenes
 
 lib = _lib.load()
 n, h = 50_000, int(os.environ.get("K2_H", 100_000))
