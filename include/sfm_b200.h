@@ -111,6 +111,21 @@ size_t sfm_fundamental_npt_workspace_bytes(int32_t n);
 int sfm_fundamental_npt(const double *d_x1, const double *d_x2, int32_t n, double *d_F,
                         void *d_ws, size_t ws_bytes, void *stream);
 
+/* Allocation-free variant of sfm_fundamental_npt. It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc). Same kernel, same result, but the 9 x n design matrix
+ * lives in a file-scope `static __device__` array inside the library instead of a caller workspace:
+ *   - limit: n <= SFM_FUNDAMENTAL_NPT_STATIC_MAX_N (16384 correspondences = 1.18 MB); every GPU that loads the
+ *     library holds that array until the process exits. Larger n returns SFM_E_WORKSPACE and leaves a message in
+ *     sfm_last_cuda_error(); use sfm_fundamental_npt with your own workspace then;
+ *   - the call itself allocates nothing (no cudaMalloc / cudaFree / allocating library routine); the array's
+ *     device address is looked up once per device on the first call with that device current, so make the first
+ *     call on each device outside stream capture;
+ *   - all calls on one device share the array, which keeps the last call's contents (the kernel overwrites what
+ *     it reads, nothing needs clearing): calls that OVERLAP on the GPU (different streams) race -- serialise them. */
+#define SFM_FUNDAMENTAL_NPT_STATIC_MAX_N 16384
+int sfm_fundamental_npt_static(const double *d_x1, const double *d_x2, int32_t n, double *d_F, void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * LM status word written by the batched solvers: (status << 16) | trial_steps, status =
  * 1 gtol, 2 ftol, 3 xtol, 5 iteration cap, -1 failed (non-finite residuals; the input is

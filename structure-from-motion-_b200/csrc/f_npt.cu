@@ -8,6 +8,8 @@
 // LAPACK-class accuracy (hard part 2). The column that converges to the
 // smallest norm gives Vt[-1].
 #include "f_math.cuh"
+#include <mutex>
+#include <stdio.h>
 
 namespace sfm {
 
@@ -230,6 +232,61 @@ extern "C" int sfm_fundamental_npt(const double *d_x1, const double *d_x2, int32
     if (ws_bytes < sfm_fundamental_npt_workspace_bytes(n)) return SFM_E_WORKSPACE;
     fundamental_npt_kernel<<<1, NPT_THREADS, 0, as_stream(stream)>>>(
         d_x1, d_x2, n, reinterpret_cast<double *>(d_ws), d_F);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+// ---- allocation-free variant (no counterpart in the reference) ----
+// Callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc) have no
+// workspace to hand over, so the 9 x n design matrix of fundamental_npt_kernel lives in a file-scope device array
+// of fixed size: 9 x 16384 doubles = 1.18 MB, held by every GPU that loads the library until the process exits.
+// The array's NAME is a host-side stand-in in host code, not a device address: the pointer the kernel gets comes
+// from cudaGetSymbolAddress, looked up once per device with that device current. All calls on a device share the
+// array (it keeps the last call's contents; the kernel writes every element it later reads, so nothing has to be
+// cleared), hence two calls that overlap on the GPU race.
+namespace sfm {
+void record_error_text(const char *msg);
+
+__device__ __align__(256) static double g_npt_static_scratch[9 * (size_t)SFM_FUNDAMENTAL_NPT_STATIC_MAX_N];
+
+constexpr int NPT_MAX_DEVICES = 64;
+static std::mutex g_npt_mu;
+static double *g_npt_scratch_ptr[NPT_MAX_DEVICES] = {};
+
+// device address of the scratch array on the CURRENT device (set up on first use); nullptr on failure
+static double *npt_static_scratch_ptr() {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { record_cuda_error(e, "cudaGetDevice(sfm_fundamental_npt_static)"); return nullptr; }
+    if (dev < 0 || dev >= NPT_MAX_DEVICES) { record_error_text("sfm_fundamental_npt_static: device ordinal out of range"); return nullptr; }
+    std::lock_guard<std::mutex> g(g_npt_mu);
+    if (!g_npt_scratch_ptr[dev]) {
+        double *ptr = nullptr;
+        e = cudaGetSymbolAddress((void **)&ptr, g_npt_static_scratch);
+        if (e != cudaSuccess || !ptr) {
+            record_cuda_error(e, "cudaGetSymbolAddress(g_npt_static_scratch)");
+            return nullptr;
+        }
+        g_npt_scratch_ptr[dev] = ptr;
+    }
+    return g_npt_scratch_ptr[dev];
+}
+}  // namespace sfm
+
+extern "C" int sfm_fundamental_npt_static(const double *d_x1, const double *d_x2, int32_t n, double *d_F,
+                                          void *stream) {
+    if (!d_x1 || !d_x2 || !d_F || n < 8) return SFM_E_INVALID;
+    if (n > SFM_FUNDAMENTAL_NPT_STATIC_MAX_N) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "sfm_fundamental_npt_static: n = %d exceeds the static scratch maximum of %d "
+                 "correspondences; use sfm_fundamental_npt with a caller workspace", (int)n,
+                 (int)SFM_FUNDAMENTAL_NPT_STATIC_MAX_N);
+        record_error_text(msg);
+        return SFM_E_WORKSPACE;
+    }
+    double *scratch = npt_static_scratch_ptr();
+    if (!scratch) return SFM_E_CUDA;
+    fundamental_npt_kernel<<<1, NPT_THREADS, 0, as_stream(stream)>>>(d_x1, d_x2, n, scratch, d_F);
     SFM_LAUNCH_CHECK();
     return SFM_OK;
 }

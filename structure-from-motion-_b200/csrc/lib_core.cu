@@ -15,6 +15,9 @@ void record_cuda_error(cudaError_t e, const char *where) {
     (void)cudaGetLastError();
 }
 
+// a validation failure that deserves words (read back through sfm_last_cuda_error like the CUDA ones)
+void record_error_text(const char *msg) { snprintf(g_err, sizeof(g_err), "%s", msg ? msg : ""); }
+
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 int sm_count() {
