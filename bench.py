@@ -157,38 +157,10 @@ def cpu_baseline_single(sc, samples, n_hyp=4000):
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU algorithm (oracle port; the Python reference cannot
-    travel to the GPU box) on all host cores, one process per core over hypothesis chunks."""
-    if rank != 0:
-        return
-    import multiprocessing as mp
-    cores = os.cpu_count() or 1
-    per_core = 48                                   # ~0.1 s per core per step at 1.9 ms/hypothesis
-    h_step = per_core * cores
-    sc, samples = make_inputs(h_step * (args.steps + args.warmup))
-    ctx = mp.get_context("fork")
-    with ctx.Pool(cores) as pool:
-        def step(i):
-            blk = samples[i * h_step:(i + 1) * h_step]
-            jobs = [(sc["x1"], sc["x2"], blk[c * per_core:(c + 1) * per_core], THRESH) for c in range(cores)]
-            t = time.perf_counter()
-            pool.map(_cpu_chunk, jobs)
-            return time.perf_counter() - t
-        for i in range(args.warmup):
-            step(i)
-        dts = [step(args.warmup + i) for i in range(args.steps)]
-    total = sum(dts)
-    value = h_step * args.steps / total
-    sample = (f"each step = {h_step} hypotheses of the same stream ({per_core}/core) over all "
-              f"{N_PTS} correspondences")
-    print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": {"workload": WORKLOAD, "threshold": THRESH, "sample": sample},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+    """--impl reference: see bench_ref.py (the reference's own CPU code from oracle/_ref, else the oracle port, on
+    all host cores; this process never imports the product package)."""
+    import bench_ref
+    bench_ref.run(args, rank, world)
 
 
 def run_ours(args, rank, world):
