@@ -74,14 +74,44 @@ def _dropin_ns():
     return ns
 
 
+def _lockstep(ns, K, log):
+    """Every bundle adjustment of the drop-in flow is ALSO run by the oracle on exactly the inputs the GPU call
+    received, and the two results are compared there. (Comparing the costs of two independent flows instead made
+    this test depend on luck: the scene keeps a few gross outliers in the tracks, so its bundle adjustments have
+    flat directions and more than one minimum, the GPU's atomics make the parameters of one converged call differ
+    by ~1e-5 along those directions from run to run, and once in several runs the NEXT call then started in the
+    basin of the other minimum -- measured: tools/pipeline_stress.py, costs 399.66 / 324.85.)"""
+    gpu_ba = ns.perform_bundle_adjustment
+
+    def both(world, have, fx, fy, flags, R_set, C_set, K_, cam_index):
+        args = (np.array(world), np.array(have), fx, fy, np.array(flags), [np.array(r) for r in R_set],
+                [np.array(c) for c in C_set], K_, cam_index)
+        Rg, Cg, Wg = gpu_ba(world, have, fx, fy, flags, R_set, C_set, K_, cam_index)
+        Rr, Cr, Wr = bo.perform_bundle_adjustment(*args)
+        sel = np.asarray(have).reshape(-1) == 1
+        reproj = 0.0
+        for i in range(len(Rg)):
+            pg = so.projection_matrix(K_, Cg[i], Rg[i]) @ np.hstack([np.asarray(Wg)[sel], np.ones((sel.sum(), 1))]).T
+            pr = so.projection_matrix(K_, Cr[i], Rr[i]) @ np.hstack([np.asarray(Wr)[sel], np.ones((sel.sum(), 1))]).T
+            reproj = max(reproj, float(np.max(np.abs(pg[:2] / pg[2] - pr[:2] / pr[2]))))
+        prob = bo.ba_build_problem(world, have, fx, fy, flags, R_set, C_set)
+        log.append(dict(gpu=_ba_cost(Wg, have, fx, fy, flags, Rg, Cg, K_), ref=_ba_cost(Wr, have, fx, fy, flags, Rr, Cr, K_),
+                        start=_ba_cost(world, have, fx, fy, flags, R_set, C_set, K_), reproj=reproj,
+                        n_obs=len(prob["cam_idx"])))
+        return Rg, Cg, Wg
+    ns.perform_bundle_adjustment = both
+    return ns
+
+
 def test_wrapper_flow_dropins_match_oracle(cuda_device):
     fx, fy, flag, K = wrapper_flow.synthetic_features()
+    ba_log = []
     with redirect_stdout(io.StringIO()), np.errstate(all="ignore"):
         random.seed(11)
         ref = wrapper_flow.run(_oracle_ns(), fx, fy, flag, K)
         state_ref = random.getstate()
         random.seed(11)
-        got = wrapper_flow.run(_dropin_ns(), fx, fy, flag, K)
+        got = wrapper_flow.run(_lockstep(_dropin_ns(), K, ba_log), fx, fy, flag, K)
         state_got = random.getstate()
     assert state_got == state_ref                               # the same draws, in the same order
     assert np.array_equal(got["filtered"], ref["filtered"])     # identical RANSAC inlier sets for all pairs
@@ -90,14 +120,17 @@ def test_wrapper_flow_dropins_match_oracle(cuda_device):
     assert rel_err(got["C2"], ref["C2"]) < 1e-6 and rel_err(got["R2"], ref["R2"]) < 1e-6
     assert rel_err(got["X12"], ref["X12"]) < 1e-6
     assert len(got["R_set"]) == len(ref["R_set"]) == fx.shape[1]          # every image was registered
-    assert len(got["ba_costs"]) == len(ref["ba_costs"]) >= 3
-    for a, b in zip(got["ba_costs"], ref["ba_costs"]):
-        assert abs(a - b) / b < 1e-6, (got["ba_costs"], ref["ba_costs"])
+    assert len(got["ba_costs"]) == len(ref["ba_costs"]) == len(ba_log) >= 3
     assert np.array_equal(got["have"], ref["have"])
-    # bundle adjustment leaves the 7-dimensional gauge free (BundleAdjustment.py:180-199): compare what is
-    # gauge invariant -- the final cost above and the reprojections
-    for i in range(fx.shape[1]):
-        sel = got["have"][:, 0] == 1
-        pg = so.projection_matrix(K, got["C_set"][i], got["R_set"][i]) @ np.hstack([got["world"][sel], np.ones((sel.sum(), 1))]).T
-        pr = so.projection_matrix(K, ref["C_set"][i], ref["R_set"][i]) @ np.hstack([ref["world"][sel], np.ones((sel.sum(), 1))]).T
-        assert np.max(np.abs(pg[:2] / pg[2] - pr[:2] / pr[2])) < 1e-2      # pixels
+    # bundle adjustment, call by call on identical inputs, by north_star's criteria: final cost within 1e-6
+    # relative, reprojection RMSE within 1e-3 px. The 7-dimensional gauge is free (BundleAdjustment.py:180-199) and
+    # the outlier-laden calls have flat directions along which scipy's own ftol = 1e-8 stop leaves ~0.02 px of slack
+    # (costs equal to 1e-9), so the individual reprojections only get a sanity bound
+    for k, e in enumerate(ba_log):
+        assert e["gpu"] < e["start"], (k, e)
+        assert abs(e["gpu"] - e["ref"]) / e["ref"] < 1e-6, (k, ba_log)
+        rmse = lambda c: np.sqrt(2.0 * c / e["n_obs"])
+        assert abs(rmse(e["gpu"]) - rmse(e["ref"])) < 1e-3, (k, ba_log)
+        assert e["reproj"] < 0.1, (k, ba_log)
+    # the first call starts from bit-comparable inputs in both flows, so there the two FLOWS must agree as well
+    assert abs(got["ba_costs"][0] - ref["ba_costs"][0]) / ref["ba_costs"][0] < 1e-6
