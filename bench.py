@@ -26,14 +26,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-N_PTS = 50_000
-N_HYP = 100_000          # per GPU (weak scaling: the hypothesis stream grows with N)
-THRESH = 0.06            # the reference default (GetInliersRANSAC.py:5, Wrapper_dev.py:105)
-DATA_SEED = 20260102
-RNG_SEED = 12345
-METRIC = "RANSAC F-hypotheses/sec"
-UNIT = "hypotheses/s"
-WORKLOAD = "C2 two-view F-RANSAC: 50k correspondences, 30% outliers, 100k hypotheses/GPU"
+from bench_config import DATA_SEED, METRIC, N_HYP, N_PTS, RNG_SEED, THRESH, UNIT, WORKLOAD  # noqa: E402
 
 
 def measured_peaks():
@@ -128,9 +121,11 @@ class ClockSampler:
 
 
 def make_inputs(n_hyp_total):
+    """The C2 scene and the reference's sample stream (random.sample from RNG_SEED, replayed bit-exactly by the
+    library's MT19937 sampler: tests/test_abi_and_sampler.py)."""
+    import bench_config
     from sfm_b200 import sampler
-    from oracle import scenes
-    sc = scenes.two_view(n=N_PTS, seed=DATA_SEED)
+    sc = bench_config.two_view_scene()
     random.seed(RNG_SEED)
     samples = sampler.sample_stream(N_PTS, 8, n_hyp_total)
     return sc, samples
@@ -156,6 +151,53 @@ def cpu_baseline_single(sc, samples, n_hyp=4000):
                       f"({dt:.1f} s)"}
 
 
+def _oracle_counts_chunk(args):
+    """Checker leg: the oracle's per-hypothesis inlier counts and F for a chunk of the stream."""
+    x1, x2, samples, thr = args
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
+    from oracle import sfm_oracle as so
+    d = so.f_ransac_detailed(x1, x2, thr, samples)
+    return np.asarray(d["counts"], np.int64), np.asarray(d["F"], np.float64).reshape(len(samples), 9)
+
+
+def parity_full_stream(pool, cores, sc, samples, gpu_counts, gpu_F, gpu_best, gpu_mask, gpu_Fbest):
+    """Benchmark-size parity (N = 1): the oracle (checker, not the thing measured) over the WHOLE hypothesis
+    stream the timed steps scored, on all host cores; compared with what the GPU produced for that stream."""
+    from oracle import sfm_oracle as so
+    t0 = time.perf_counter()
+    h = len(samples)
+    per = max(64, -(-h // (cores * 8)))
+    jobs = [(sc["x1"], sc["x2"], samples[a:a + per], THRESH) for a in range(0, h, per)]
+    res = pool.map(_oracle_counts_chunk, jobs, chunksize=1)
+    counts = np.concatenate([r[0] for r in res])
+    F = np.concatenate([r[1] for r in res])
+    dt = time.perf_counter() - t0
+    best = int(np.argmax(counts))                      # first maximum == the reference's strict '>' rule
+    err = so.f_errors(F[best].reshape(3, 3), sc["x1"], sc["x2"])
+    band = np.abs(err - THRESH) < 1e-9
+    mask_ref = err < THRESH
+    mism = np.nonzero(counts != gpu_counts)[0]
+    explained = 0
+    for k in mism[:200]:                               # a count may differ only through points in the 1e-9 band
+        e = so.f_errors(F[k].reshape(3, 3), sc["x1"], sc["x2"])
+        explained += int(abs(int(counts[k]) - int(gpu_counts[k])) <= int((np.abs(e - THRESH) < 1e-9).sum()))
+    nrm = np.linalg.norm(F, axis=1)
+    rel = np.linalg.norm(gpu_F - F, axis=1) / np.where(nrm > 0, nrm, 1.0)
+    scoring = counts > 0                               # hypotheses that can win at all
+    return {"checker": "oracle/sfm_oracle.f_ransac_detailed over the whole stream", "hypotheses_checked": int(h),
+            "oracle_seconds": dt, "oracle_cores": cores, "oracle_hypotheses_s": h / dt,
+            "winner_equal": bool(best == int(gpu_best[0]) and int(counts[best]) == int(gpu_best[1])),
+            "winner": [best, int(counts[best])], "count_mismatches": int(len(mism)),
+            "count_mismatches_explained_by_band": int(explained),
+            "band_population": int(band.sum()),
+            "mask_equal_outside_1e-9": bool(np.array_equal(gpu_mask[~band].astype(bool), mask_ref[~band])),
+            "rel_F_winner": float(np.linalg.norm(gpu_Fbest.ravel() - F[best]) / np.linalg.norm(F[best])),
+            "frac_hypotheses_rel_F_below_1e-6": float(np.mean(rel < 1e-6)),
+            "max_rel_F_over_scoring_hypotheses": float(rel[scoring].max()) if scoring.any() else None,
+            "note": "F of a (near-)degenerate 8-point sample is an ill-conditioned null vector: hypotheses whose F "
+                    "differs beyond 1e-6 are listed by fraction; counts are compared for ALL hypotheses"}
+
+
 def run_reference(args, rank, world):
     """--impl reference: see bench_ref.py (the reference's own CPU code from oracle/_ref, else the oracle port, on
     all host cores; this process never imports the product package)."""
@@ -169,6 +211,12 @@ def run_ours(args, rank, world):
     from sfm_b200 import _lib, device, ransac
 
     local = int(os.environ.get("LOCAL_RANK", 0))
+    # the checker's process pool is forked BEFORE this process touches CUDA; it stays idle during every timed region
+    cores = os.cpu_count() or 1
+    pool = None
+    if world == 1 and not args.skip_parity:
+        import multiprocessing as mp
+        pool = mp.get_context("fork").Pool(cores)
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -229,26 +277,24 @@ def run_ours(args, rank, world):
     achieved = alg_bytes / (k2_ms * 1e-3) / 1e9
     tests = float(N_PTS) * N_HYP
     fma_peak = 148 * 128 * 1.965e9          # FP32 FMA lanes x clock: 119-125 of 128 per clock and SM measured
-    roofline = {"bound": "hbm", "kernel": "f_score_packed_kernel (K2)", "achieved": achieved,
-                "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                "traffic": _ncu_traffic("f_score_packed_kernel"), "peak_source": peak_src, "kernel_ms": k2_ms,
-                "algorithmic_bytes_per_launch": alg_bytes,
-                "note": "algorithmic bytes = (32 B x N + 76 B) per hypothesis (SURVEY 8d): what a kernel without "
-                        "on-chip reuse would stream. The 1.6 MB correspondence set is staged in shared memory "
-                        "and re-read by every hypothesis tile, so frac > 1 is the on-chip reuse factor, not an "
-                        "HBM fraction (traffic = DRAM bytes per launch from the ncu capture under profiles/); the physical "
-                        "limiter is the "
-                        "FP32 FMA pipe: see fp32_pipe",
-                "fp32_pipe": {"fma_lane_ops_per_test": 23,
-                              "what": "certified FP32 filter on packed FFMA2/FMUL2/FADD2: 23 packed instructions "
-                                      "per pair of tests = 23 FMA-lane operations per test, + 2 MUFU.SQRT; 2e-4 of "
-                                      "the tests are redone in FP64",
-                              "tests_per_launch": tests,
-                              "achieved_tlaneops_s": 23.0 * tests / (k2_ms * 1e-3) / 1e12,
-                              "peak_tlaneops_s": fma_peak / 1e12,
-                              "frac": 23.0 * tests / (k2_ms * 1e-3) / fma_peak,
-                              "peak_source": "148 SMs x 128 FP32 lanes x 1.965 GHz; profiles/r01_ubench_fp32_b200.txt "
-                                             "measures 119 (FFMA) and 125 (FFMA2, broadcast operands) of 128"}}
+    lane_ops = 23.0 * tests / (k2_ms * 1e-3)
+    roofline = {"bound": "fp32_pipe", "kernel": "f_score_packed_kernel (K2)", "achieved": lane_ops / 1e12,
+                "peak": fma_peak / 1e12, "unit": "T FMA-lane-op/s", "frac": lane_ops / fma_peak,
+                "traffic": _ncu_traffic("f_score_packed_kernel"), "kernel_ms": k2_ms,
+                "peak_source": "148 SMs x 128 FP32 lanes x 1.965 GHz (max SM clock); profiles/r01_ubench_fp32_b200.txt "
+                               "measures 119 (FFMA) and 125 (FFMA2, broadcast operands) of 128 lanes per clock and SM",
+                "what": "certified FP32 filter on packed FFMA2/FMUL2/FADD2: 23 FMA-lane operations + 2 MUFU.SQRT per "
+                        "(hypothesis, correspondence) test; 2e-4 of the tests are redone in FP64; tests per launch "
+                        "= N x H",
+                "tests_per_launch": tests,
+                "why_not_hbm": "the 1.6 MB correspondence set is staged in shared memory and re-read by every "
+                               "hypothesis tile: DRAM traffic per launch (`traffic`, ncu) is ~1e-4 of the algorithmic "
+                               "bytes below, so HBM cannot be the bound",
+                "hbm_algorithmic": {"bytes_per_launch": alg_bytes, "achieved_gbs": achieved, "peak_gbs": peaks["hbm_gbs"],
+                                    "ratio": achieved / peaks["hbm_gbs"], "peak_source": peak_src,
+                                    "note": "(32 B x N + 76 B) per hypothesis (SURVEY 8d): what a kernel without "
+                                            "on-chip reuse would stream; ratio > 1 is the reuse factor, NOT a "
+                                            "roofline fraction"}}
 
     # end to end through the drop-in signature: host numpy in, host numpy out, RNG replay, H2D, D2H
     index = np.arange(N_PTS)
@@ -270,6 +316,26 @@ def run_ours(args, rank, world):
            "steps": e2e_steps}
 
     best = r.best.cpu().numpy()
+    parity = None
+    if world == 1 and pool is not None:
+        parity = parity_full_stream(pool, cores, sc, samples_all, plan.r.counts.cpu().numpy().astype(np.int64),
+                                    plan.r.F.cpu().numpy(), best, plan.r.mask.cpu().numpy(),
+                                    plan.r.F_best.cpu().numpy())
+        pool.close()
+        pool.join()
+    elif world > 1:
+        # the sharded run against ONE GPU scoring the whole stream (rank 0, outside every timed region)
+        if rank == 0:
+            whole = ransac.FRansacPlan(N_PTS, N_HYP * world)
+            r1 = whole.run(d_x, d_s_all, THRESH)
+            b1 = r1.best.cpu().numpy()
+            parity = {"checker": "the same stream scored by one GPU (sfm_f_ransac over all N x 100k hypotheses)",
+                      "parity_vs_n1": {"winner_equal": bool(b1[0] == best[0] and b1[1] == best[1]),
+                                       "winner_n1": [int(b1[0]), int(b1[1])],
+                                       "mask_equal": bool(torch.equal(r1.mask, r.mask)),
+                                       "F_best_bit_equal": bool(torch.equal(r1.F_best, r.F_best))}}
+            del whole, r1
+        dist.barrier()
     ba_mgpu = None
     if world > 1 and not args.skip_ba:
         import bench_ba
@@ -284,6 +350,8 @@ def run_ours(args, rank, world):
                           "winner": [int(best[0]), int(best[1])]},
                "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches),
                "clocks": clocks.summary()}
+        if parity is not None:
+            out["parity"] = parity
         if world == 1:
             out["cpu_baseline"] = cpu_baseline_single(sc, samples_all, n_hyp=args.cpu_hyp)
             if not args.skip_ba:
@@ -318,6 +386,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-hyp", type=int, default=6000, help="hypotheses in the 1-core CPU baseline sample")
     ap.add_argument("--skip-ba", action="store_true", help="F-RANSAC part only")
+    ap.add_argument("--skip-parity", action="store_true", help="no oracle pass over the whole hypothesis stream")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

@@ -15,8 +15,7 @@ import time
 
 import numpy as np
 
-C3 = dict(n_cams=50, n_pts=20_000, obs_per_pt=10, seed=20260103, layout="arc", window=None)
-C5 = dict(n_cams=1000, n_pts=500_000, obs_per_pt=8, seed=20260106, layout="ring", window=40)
+from bench_config import C3, C5  # noqa: E402
 
 
 def _scene(cfg):
@@ -69,6 +68,11 @@ def time_pass(prob, cams0, pts0, which, reps, flush):
         b.record()
     torch.cuda.synchronize()
     return sum(a.elapsed_time(b) for a, b in ev) / reps
+
+
+def device_copy(a):
+    from sfm_b200 import device
+    return device.to_device(np.ascontiguousarray(a))
 
 
 def k9p_bytes(n_obs, n_pts):
@@ -151,6 +155,9 @@ def run_single_gpu(args, peaks, peak_src, flush):
                   "d2h_bytes_per_step": int(cams0.nbytes + pts0.nbytes + 64),
                   "api": "sfm_b200.bundle.ba_solve_sparse(cams, pts, cam_idx, pt_idx, obs, K): host numpy in/out, "
                          "includes workspace allocation, H2D, index build, solve, D2H", "steps": e2e_steps}
+    d_c, d_p = device_copy(cams0), device_copy(pts0)
+    prob.solve_device(d_c, d_p, profile=True)
+    out["phase_ms_per_solve"] = bundle.last_profile()
     del prob
     # ---- C5 on one GPU: roofline evidence for the streaming passes ----
     sc5, cams5, pts5 = _scene(C5)
@@ -165,11 +172,15 @@ def run_single_gpu(args, peaks, peak_src, flush):
         t_ms = time_pass(prob5, cams5, pts5, which, 10, flush)
         gbs = nbytes / (t_ms * 1e-3) / 1e9
         passes[name] = {"ms": t_ms, "algorithmic_bytes": nbytes, "achieved_gbs": gbs, "frac_of_measured_hbm": gbs / peaks["hbm_gbs"]}
+    d_c, d_p = device_copy(cams5), device_copy(pts5)
+    prob5.solve_device(d_c, d_p, profile=True)
+    c5_phases = bundle.last_profile()
     k9 = passes["K9p ba_point_pass_kernel"]
     out["c5_single_gpu"] = {"workload": "C5 synthetic BAL-scale BA on ONE GPU: " + _name(C5),
                             "value": its5 / (ms5 * 1e-3), "unit": "LM iterations/s", "ms_per_solve": ms5 / 3,
                             "lm_iterations_per_solve": its5 / 3, "cost": infos5[-1]["cost"],
-                            "rmse_px": float(np.sqrt(2 * infos5[-1]["cost"] / n5)), "passes": passes}
+                            "rmse_px": float(np.sqrt(2 * infos5[-1]["cost"] / n5)), "passes": passes,
+                            "phase_ms_per_solve": c5_phases}
     out["roofline"] = {"bound": "hbm", "kernel": "ba_point_pass_kernel (K9p) on C5", "achieved": k9["achieved_gbs"],
                        "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": k9["frac_of_measured_hbm"],
                        # dram__bytes_read.sum + dram__bytes_write.sum of this kernel on this workload, one
@@ -183,16 +194,30 @@ def run_single_gpu(args, peaks, peak_src, flush):
 
 def run_sharded(args, rank, world, flush):
     """N > 1: BASELINE configs[4] (C5) sharded by point across the ranks; strong scaling (the problem
-    is fixed, each rank holds 1/N of the points). Time = max over ranks of the CUDA-event time."""
+    is fixed, each rank holds 1/N of the points). Time = max over ranks of the CUDA-event time. Rank 0 first
+    solves the WHOLE problem alone (outside the timed region): the one-GPU figure of the same run on the same
+    box, and the parity reference for the sharded result."""
     import torch
     import torch.distributed as dist
-    from sfm_b200 import _lib, bundle_mgpu, device
+    from sfm_b200 import _lib, bundle, bundle_mgpu, device
     comm = bundle_mgpu.NcclComm(rank, world)
     sc, cams0, pts0 = _scene(C5)
+    steps = max(3, min(args.steps, 5))
+    n1 = None
+    if rank == 0:
+        whole = bundle.BAProblem(C5["n_cams"], C5["n_pts"], sc["cam_idx"], sc["pt_idx"], sc["obs"], sc["K"])
+        ms1, infos1 = time_solves(whole, cams0, pts0, steps, 2, flush)
+        d_c1, d_p1 = device_copy(cams0), device_copy(pts0)
+        whole.solve_device(d_c1, d_p1)
+        n1 = dict(value=sum(i["n_linearisations"] for i in infos1) / (ms1 * 1e-3), ms_per_solve=ms1 / steps,
+                  cost=infos1[-1]["cost"], cams=d_c1.cpu().numpy(), pts=d_p1.cpu().numpy())
+        del whole, d_c1, d_p1
+        bundle.release_cache()
+        torch.cuda.empty_cache()
+    dist.barrier()
     prob = bundle_mgpu.BAShardedProblem(C5["n_cams"], C5["n_pts"], sc["cam_idx"], sc["pt_idx"], sc["obs"], sc["K"], comm)
     d_cam0, d_pts0 = device.to_device(cams0), device.to_device(pts0[prob.p_lo:prob.p_hi])
     d_cam, d_pts = torch.empty_like(d_cam0), torch.empty_like(d_pts0)
-    steps = max(3, min(args.steps, 5))
     for _ in range(2):
         d_cam.copy_(d_cam0); d_pts.copy_(d_pts0)
         prob.solve_device(d_cam, d_pts)
@@ -208,20 +233,37 @@ def run_sharded(args, rank, world, flush):
         b.record()
         ev.append((a, b))
     dist.barrier(); torch.cuda.synchronize()
+    launches = int(_lib.launch_count() - l0)
     t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], dtype=torch.float64, device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
+    # one more solve with the phase profile on (not timed)
+    d_cam.copy_(d_cam0); d_pts.copy_(d_pts0)
+    prob.solve_device(d_cam, d_pts, profile=True)
+    phases = bundle.last_profile()
     its = sum(i["n_linearisations"] for i in infos)
     n5 = len(sc["obs"])
+    value = its / (ms * 1e-3)
     out = {"metric": "BA LM iterations/sec", "unit": "LM iterations/s", "dtype": "f64", "scaling": "strong",
-           "value": its / (ms * 1e-3), "ms_per_solve": ms / steps, "solves": steps, "n_gpus": world,
+           "value": value, "ms_per_solve": ms / steps, "solves": steps, "n_gpus": world,
            "config": {"workload": "C5 synthetic BAL-scale BA sharded by point: " + _name(C5),
                       "points_per_rank": prob.n_pts, "observations_per_rank": prob.n_obs,
-                      "collectives_per_trial": "all-reduce of the packed lower block triangle of S + g_red (%.0f MB), "
-                                               "6 scalars, gmax; per linearisation U|g_c|cost"
-                                               % ((48 * 48 * 125 * 126 / 2 + 6000) * 8 / 1e6)},
+                      "collectives_per_trial": "all-reduce of the blocks of S some rank touches + g_red (bytes below), "
+                                               "6 scalars, gmax; per linearisation U|g_c|cost",
+                      "s_allreduce_bytes_per_trial": phases["s_allreduce_bytes_per_trial"]},
            "lm_iterations_per_solve": its / steps, "cost": infos[-1]["cost"],
            "rmse_px": float(np.sqrt(2 * infos[-1]["cost"] / n5)), "status": infos[-1]["status"],
-           "gpu_launches": int(_lib.launch_count() - l0)}
+           "gpu_launches": launches, "phase_ms_per_solve_rank0": phases}
+    if rank == 0:
+        cams = d_cam.cpu().numpy()
+        pts_local = d_pts.cpu().numpy()
+        out["n1_value"] = n1["value"]
+        out["n1_ms_per_solve"] = n1["ms_per_solve"]
+        out["efficiency_vs_n1"] = value / (world * n1["value"])
+        out["speedup_vs_n1"] = value / n1["value"]
+        out["parity_vs_n1"] = {"cost_rel": abs(infos[-1]["cost"] - n1["cost"]) / n1["cost"],
+                               "cameras_max_abs": float(np.max(np.abs(cams - n1["cams"]))),
+                               "points_rank0_max_abs": float(np.max(np.abs(pts_local - n1["pts"][prob.p_lo:prob.p_hi]))),
+                               "what": "the sharded solve against rank 0 solving the whole problem alone in this run"}
     comm.destroy()
     return out

@@ -181,7 +181,7 @@ typedef struct sfm_ba_options {
     double lambda0;      /* initial damping of (J^T J + lambda D^2); D = Jacobian column norms */
     int32_t reuse_index; /* 1: d_ws still holds the camera-major index of a previous sfm_ba_solve call
                             on the SAME d_cam_idx / d_pt_idx contents (skips the index build) */
-    int32_t reserved;
+    int32_t reserved;    /* bit 0: record the phase profile of this solve (sfm_ba_last_profile) */
 } sfm_ba_options;
 
 typedef struct sfm_ba_result {
@@ -204,6 +204,14 @@ size_t sfm_ba_workspace_bytes(int32_t n_cams, int32_t n_pts, int32_t n_obs);
  * library); the next solve rebuilds what it needs. Returns the number of bytes released through *bytes
  * (may be NULL). */
 int sfm_ba_release_cache(uint64_t *bytes, void *stream);
+
+/* Phase profile of the last sfm_ba_solve* call of this process that ran with opts.reserved bit 0 set (CUDA events
+ * on the caller's stream; diagnostic, used by bench.py for the multi-GPU time breakdown). HOST out, milliseconds
+ * summed over the solve: [0] Schur complement (K10*), [1] all-reduce of S / g_red incl. pack + unpack (0 on one
+ * GPU), [2] camera solve K11, [3] rest of the trial steps (back substitution, update, cost pass, scalar
+ * all-reduce), [4] linearisations (K9, incl. their all-reduce); then [5] trial steps, [6] linearisations,
+ * [7] bytes all-reduced for S / g_red per trial step. */
+int sfm_ba_last_profile(double *h_out8);
 
 /* K8 alone: residual vector of bundle_adjustment_residuals (BundleAdjustment.py:43-110),
  * d_r [n_obs,2] interleaved [du,dv] = observed - projected (may be null), d_cost[0] = 0.5 |r|^2

@@ -75,8 +75,9 @@ class BAProblem:
         _lib.check(rc, "sfm_ba_linearise")
         self._indexed = True
 
-    def solve_device(self, d_cam, d_pts, max_nfev=BA_MAX_NFEV, tol=REF_TOL, lambda0=1e-4, verbose=False):
-        """K8-K12 LM; d_cam [n_cams,6] and d_pts [n_pts,3] are refined in place. Returns a dict."""
+    def solve_device(self, d_cam, d_pts, max_nfev=BA_MAX_NFEV, tol=REF_TOL, lambda0=1e-4, verbose=False, profile=False):
+        """K8-K12 LM; d_cam [n_cams,6] and d_pts [n_pts,3] are refined in place. Returns a dict.
+        profile: record the phase times of this solve (read them with last_profile())."""
         lib = _lib.load()
         opts = _lib.BAOptions()
         lib.sfm_ba_default_options(C.addressof(opts))
@@ -84,6 +85,7 @@ class BAProblem:
         opts.ftol = opts.xtol = opts.gtol = float(tol)
         opts.lambda0 = float(lambda0)
         opts.reuse_index = int(self._indexed)
+        opts.reserved = 1 if profile else 0
         res = _lib.BAResult()
         rc = lib.sfm_ba_solve(
             device.ptr(d_cam), device.ptr(d_pts), device.ptr(self.d_obs), device.ptr(self.d_cam_idx),
@@ -93,6 +95,15 @@ class BAProblem:
         self._indexed = True
         return dict(cost0=res.cost0, cost=res.cost, gnorm=res.gnorm, lambda_=res.lambda_, status=res.status,
                     n_linearisations=res.n_linearisations, n_trials=res.n_trials, n_chol_fail=res.n_chol_fail)
+
+
+def last_profile() -> dict:
+    """Phase times [ms] of the last solve that ran with profile=True (sfm_ba_last_profile)."""
+    out = np.zeros(8)
+    _lib.check(_lib.load().sfm_ba_last_profile(out.ctypes.data), "sfm_ba_last_profile")
+    return dict(schur_ms=out[0], s_allreduce_ms=out[1], camera_solve_k11_ms=out[2], trial_rest_ms=out[3],
+                linearise_ms=out[4], trial_steps=int(out[5]), linearisations=int(out[6]),
+                s_allreduce_bytes_per_trial=int(out[7]))
 
 
 def release_cache() -> int:

@@ -107,13 +107,15 @@ class BAShardedProblem:
         self.ws = device.empty((self.ws_bytes,), torch.uint8)
         self._indexed = False
 
-    def solve_device(self, d_cam, d_pts_local, max_nfev=BA_MAX_NFEV, tol=REF_TOL, lambda0=1e-4, verbose=False):
+    def solve_device(self, d_cam, d_pts_local, max_nfev=BA_MAX_NFEV, tol=REF_TOL, lambda0=1e-4, verbose=False,
+                     profile=False):
         lib = _lib.load()
         opts = _lib.BAOptions()
         lib.sfm_ba_default_options(C.addressof(opts))
         opts.max_trials, opts.verbose = int(max_nfev), int(bool(verbose) and self.comm.rank == 0)
         opts.ftol = opts.xtol = opts.gtol = float(tol)
         opts.lambda0, opts.reuse_index = float(lambda0), int(self._indexed)
+        opts.reserved = 1 if profile else 0
         res = _lib.BAResult()
         rc = lib.sfm_ba_solve_mgpu(
             device.ptr(d_cam), device.ptr(d_pts_local), device.ptr(self.d_obs), device.ptr(self.d_cam_idx),

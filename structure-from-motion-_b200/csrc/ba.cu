@@ -1817,6 +1817,7 @@ extern "C" size_t sfm_ba_workspace_bytes(int32_t n_cams, int32_t n_pts, int32_t 
 }
 
 static bool g_attrs_set = false;
+static double g_ba_prof[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
 struct PlanKey {
     const void *ws, *cam_idx;
@@ -2124,8 +2125,13 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
         return SFM_OK;
     };
 
+    static thread_local cudaEvent_t pe_lin0[2] = {};
+    const bool prof0 = (o.reserved & 1) != 0;
+    if (prof0 && !pe_lin0[0]) { SFM_CUDA_TRY(cudaEventCreate(&pe_lin0[0])); SFM_CUDA_TRY(cudaEventCreate(&pe_lin0[1])); }
+    if (prof0) cudaEventRecord(pe_lin0[0], st);
     if ((rc = launch_cam_linearise(pl, K, pl.cam[0], pl.camlin[0], st)) != SFM_OK) return rc;
     if ((rc = linearise(1)) != SFM_OK) return rc;
+    if (prof0) cudaEventRecord(pe_lin0[1], st);
     SFM_CUDA_TRY(cudaMemcpyAsync(h_scal, pl.red1, sizeof(double), cudaMemcpyDeviceToHost, st));
     SFM_CUDA_TRY(cudaStreamSynchronize(st));
     double cost = h_scal[0];
@@ -2136,11 +2142,22 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
         return SFM_OK;
     }
 
+    // opts.reserved bit 0: phase profile of this solve (CUDA events on the caller's stream, read at the host
+    // synchronisation every trial step already has): sfm_ba_last_profile()
+    const bool prof = (o.reserved & 1) != 0;
+    static thread_local cudaEvent_t pe[7] = {};
+    if (prof && !pe[0])
+        for (int i = 0; i < 7; ++i) SFM_CUDA_TRY(cudaEventCreate(&pe[i]));
+    double pacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool lin_pending = false;
+    auto mark = [&](int i) { if (prof) cudaEventRecord(pe[i], st); };
+    auto span = [&](int a, int b) { float ms = 0.f; cudaEventElapsedTime(&ms, pe[a], pe[b]); return (double)ms; };
     double lambda = o.lambda0 > 0 ? o.lambda0 : 1e-4, nu = 2.0, xnorm = 0.0;
     int status = -2, trials = 0, first_lin = 1, update_D = 1, chol_fail = 0;
     const size_t s_bytes = sizeof(double) * (size_t)(pl.npad + BA_NB) * pl.ld;
     while (status == -2) {
         // ---- one trial step with damping lambda ----
+        mark(0);
         SFM_CUDA_TRY(cudaMemsetAsync(pl.S, 0, s_bytes, st));
         SFM_CUDA_TRY(cudaMemsetAsync(pl.flags + 1, 0, 2 * sizeof(int), st));
         SFM_CUDA_TRY(cudaMemsetAsync(pl.tp, 0, sizeof(double) * 3 * (size_t)np, st));
@@ -2217,6 +2234,7 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
                                                              pl.S + (size_t)pl.npad * pl.ld, pl.gmax, pl.flags + 1);
             SFM_LAUNCH_CHECK();
         }
+        mark(1);
         if (comm && blk_list) {
             const size_t packed = (size_t)n_blk * 36 + n;
             const unsigned grid = (unsigned)((packed + 255) / 256);
@@ -2234,6 +2252,7 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
             SFM_LAUNCH_CHECK();
         }
         if (update_D && (rc = comm_allreduce_max_u64(comm, pl.gmax, 1, st)) != SFM_OK) return rc;
+        mark(2);
         static unsigned long long *d_cprof = nullptr;          // SFM_BA_CHOL_PROF=1: K11 phase profile (diagnostic)
         static int cprof = -1;
         if (cprof < 0) {
@@ -2244,6 +2263,7 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
         if (dag) rc = chol_dag_launch(dag, pl.S, pl.ld, pl.npad, pl.dc, pl.flags + 2, st);
         else rc = chol_solve_launch(pl.S, pl.ld, pl.npad, pl.Linv, pl.dc, pl.flags + 2, st, cprof ? d_cprof : nullptr);
         if (rc != SFM_OK) return rc;
+        mark(3);
         if (cprof) {
             unsigned long long hp[8];
             cudaStreamSynchronize(st);
@@ -2266,8 +2286,13 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
                                                     pl.flags + 1, pl.flags + 2, pl.scal);
         SFM_LAUNCH_CHECK();
         if ((rc = comm_allreduce_sum_f64(comm, pl.scal, 6, st)) != SFM_OK) return rc;
+        mark(4);
         SFM_CUDA_TRY(cudaMemcpyAsync(h_scal, pl.scal, 8 * sizeof(double), cudaMemcpyDeviceToHost, st));
         SFM_CUDA_TRY(cudaStreamSynchronize(st));
+        if (prof) {
+            pacc[0] += span(0, 1); pacc[1] += span(1, 2); pacc[2] += span(2, 3); pacc[3] += span(3, 4);
+            if (lin_pending) { pacc[4] += span(5, 0); lin_pending = false; }
+        }
         ++trials;
         const double cost_new = h_scal[0], sg = h_scal[1], Ds2 = h_scal[2], Dx2n = h_scal[3], Dx2c = h_scal[4];
         const double gmax = h_scal[6];
@@ -2316,18 +2341,36 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
         if (accept) {
             first_lin = 0;
             update_D = 1;
+            mark(5);
             if ((rc = linearise(0)) != SFM_OK) return rc;
+            lin_pending = prof;
             h_result->n_linearisations += 1;
         }
     }
     SFM_CUDA_TRY(cudaMemcpyAsync(d_cam, pl.cam[cur], sizeof(double) * 6 * nc, cudaMemcpyDeviceToDevice, st));
     SFM_CUDA_TRY(cudaMemcpyAsync(d_pts, pl.pts[cur], sizeof(double) * 3 * (size_t)np, cudaMemcpyDeviceToDevice, st));
     SFM_CUDA_TRY(cudaStreamSynchronize(st));
+    if (prof) {
+        float ms0 = 0.f;
+        cudaEventElapsedTime(&ms0, pe_lin0[0], pe_lin0[1]);
+        pacc[4] += ms0;
+        pacc[5] = trials; pacc[6] = h_result->n_linearisations;
+        pacc[7] = blk_list ? ((double)n_blk * 36 + n) * 8.0 : (comm ? (double)(s_pack_offset(pl.npad, pl.npad) + pl.npad) * 8.0 : 0.0);
+        std::lock_guard<std::mutex> g(g_plan_mu);
+        for (int i = 0; i < 8; ++i) g_ba_prof[i] = pacc[i];
+    }
     h_result->cost = cost;
     h_result->status = status;
     h_result->n_trials = trials;
     h_result->n_chol_fail = chol_fail;
     h_result->lambda = lambda;
+    return SFM_OK;
+}
+
+extern "C" int sfm_ba_last_profile(double *h_out8) {
+    if (!h_out8) return SFM_E_INVALID;
+    std::lock_guard<std::mutex> g(g_plan_mu);
+    for (int i = 0; i < 8; ++i) h_out8[i] = g_ba_prof[i];
     return SFM_OK;
 }
 
