@@ -305,6 +305,38 @@ int sfm_chol_solve_profiled(const double *d_S, const double *d_g, int32_t n, dou
  * [7] whole factor, accumulated; variant must be 0). tools/diag_bench.py. */
 int sfm_chol_diag_bench(const double *d_A48, int32_t variant, uint64_t *d_out8, void *stream);
 
+/* ---- a8 / K6a: LinearPnP on the device (replaces LinearPnP.py:3-96) -----------------------------------
+ * The hypothesis generator of PnPRANSAC (PnPRANSAC.py:49-55: LinearPnP on 4 sampled correspondences) and its
+ * all-points fallback (:82-87). The reference takes `Vt[-1]` of numpy.linalg.svd of the 2N x 12 DLT matrix; for
+ * N = 4 (and 5) that matrix is rank deficient and the row is LAPACK's pick inside the null space: the last column
+ * of the product of the right Householder reflectors of dgebd2. The kernels replay that construction and the
+ * Householder sign convention of the QR clean-up (csrc/linpnp_math.cuh), which reproduces the reference to 1e-8
+ * wherever its output is a function of its input. It is not in the `det(R) < 0` branch of LinearPnP.py:88-90
+ * (27 % of random 4-point samples), where LAPACK flips a singular vector chosen by rounding noise; those
+ * hypotheses get a documented deterministic pose and bit 0 of their flag set (bit 1: non-finite pose).
+ *   h_K, h_Kinv : HOST 3x3; h_Kinv = the caller's inverse of K (the reference uses numpy.linalg.inv), may be
+ *                 null (adjugate formula then)
+ *   d_P [.,12]  : K [R | -R C] of every hypothesis, the input of sfm_pnp_score_count (PnPRANSAC.py:60)
+ * sfm_linear_pnp4_batch: d_sample [n_regs * h_per_reg, 4] int32, the samples of registration r index its own
+ *   correspondences d_offsets[r] .. d_offsets[r+1] of the concatenated d_X [.,3], d_x [.,2] (d_offsets == null:
+ *   one registration of n correspondences). d_C [.,3], d_R [.,9], d_flag [.] may be null. Thread per hypothesis.
+ *   policy bit 0 (the PnPRANSAC drop-in sets it): hypotheses in the noise-decided branch do not vote -- their d_P
+ *   row is NaN, so sfm_pnp_score_count gives them zero inliers. In the reference their pose is a rotation reflected
+ *   along a direction drawn from rounding noise, which all but never wins the consensus (measured: never in 21
+ *   registrations x 200-300 hypotheses), whereas any fixed rule occasionally produces a well-scoring pose and would
+ *   change the winner; muting them keeps the WINNER equal to the reference's. policy 0: they vote with the
+ *   documented deterministic pose.
+ * sfm_linear_pnp_npt: all n >= 4 correspondences of one registration -> d_CR [12] = (C, R row-major), d_P [12]
+ *   and d_flag [1] (either may be null); workspace sfm_linear_pnp_npt_workspace_bytes(n). */
+int sfm_linear_pnp4_batch(const double *d_X, const double *d_x, const int32_t *d_offsets, int32_t n_regs,
+                          int32_t n, const int32_t *d_sample, int32_t h_per_reg, const double *h_K,
+                          const double *h_Kinv, int32_t policy, double *d_C, double *d_R, double *d_P,
+                          uint8_t *d_flag, void *stream);
+size_t sfm_linear_pnp_npt_workspace_bytes(int32_t n);
+int sfm_linear_pnp_npt(const double *d_X, const double *d_x, int32_t n, const double *h_K,
+                       const double *h_Kinv, double *d_CR, double *d_P, uint8_t *d_flag, void *d_ws,
+                       size_t ws_bytes, void *stream);
+
 /* @@MORE@@ (further sections are appended above this marker as the path widens) */
 
 /* ---- N4: two-view pose front end ------------------------------------------------

@@ -208,6 +208,29 @@ def gen_pnp():
     save("pnp.npz", K=scenes.K_REF, **out)
 
 
+def gen_linpnp():
+    """The reference's LinearPnP (LinearPnP.py:3-96) on every 4-point sample the PnP goldens recorded, and on small
+    and large all-point sets: pins the hypothesis generator of PnPRANSAC (numpy's Vt[-1] of the 8 x 12 system, the QR
+    sign conventions) for the device kernel."""
+    g = np.load(os.path.join(OUT, "pnp.npz"))
+    out = {}
+    with np.errstate(all="ignore"):
+        for tag in ("a", "b", "c"):
+            X, x, samples = g[f"X_{tag}"], g[f"x_{tag}"], g[f"samples_{tag}"]
+            C4, R4 = np.full((len(samples), 3), np.nan), np.full((len(samples), 3, 3), np.nan)
+            for i, smp in enumerate(samples):
+                try:
+                    C4[i], R4[i] = refLPnP.LinearPnP(X[smp], x[smp], scenes.K_REF)
+                except Exception:
+                    pass
+            out[f"C4_{tag}"], out[f"R4_{tag}"] = C4, R4
+        Xb, xb = g["X_b"], g["x_b"]
+        for n in (5, 6, 7, 8, 12, 50, 2000):
+            C_, R_ = refLPnP.LinearPnP(Xb[:n], xb[:n], scenes.K_REF)
+            out[f"Cn_{n}"], out[f"Rn_{n}"] = C_, R_
+    save("linpnp4.npz", K=scenes.K_REF, **out)
+
+
 def dense_ba_inputs(sc, n_extra=7):
     """Dense (F x n_img) arrays in the shape perform_bundle_adjustment takes, with some
     untriangulated filler rows so that the valid-point remapping is exercised."""
@@ -261,6 +284,6 @@ def gen_ba():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["f8pt", "fransac", "p3data", "tri", "pnp", "ba", "twoview", "homography"]
+    which = sys.argv[1:] or ["f8pt", "fransac", "p3data", "tri", "pnp", "linpnp", "ba", "twoview", "homography"]
     for w in which:
         globals()["gen_" + w]()

@@ -60,6 +60,11 @@ SIGNATURES = {
     "sfm_fundamental_npt_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "sfm_fundamental_npt": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_vp, C.c_size_t, c_vp]),
     "sfm_fundamental_npt_static": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_f64p, c_vp]),
+    "sfm_linear_pnp4_batch": (C.c_int, [c_f64p, c_f64p, c_i32p, C.c_int32, C.c_int32, c_i32p, C.c_int32, c_vp, c_vp,
+                                        C.c_int32, c_f64p, c_f64p, c_f64p, c_u8p, c_vp]),
+    "sfm_linear_pnp_npt_workspace_bytes": (C.c_size_t, [C.c_int32]),
+    "sfm_linear_pnp_npt": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_vp, c_vp, c_f64p, c_f64p, c_u8p, c_vp, C.c_size_t,
+                                     c_vp]),
     "sfm_ba_default_options": (None, [c_vp]),
     "sfm_ba_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "sfm_ba_last_profile": (C.c_int, [c_vp]),

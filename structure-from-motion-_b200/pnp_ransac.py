@@ -1,11 +1,8 @@
-"""Host side of PnP RANSAC: mirrors PnPRANSAC.py:6-89 and LinearPnP.py:3-96.
-
-Consensus scoring and the first-maximum argmax run on the GPU (K6 + K3). Hypothesis generation
-(LinearPnP on 4-point samples) stays on the host for now: with 4 points the 8x12 DLT system has a
-4-dimensional null space and the reference's Vt[-1] is whatever LAPACK's dgesdd returns (SURVEY.md
-8.1-Q6), so hypothesis parity is only defined by calling the same LAPACK routine on the same
-matrix; this module does exactly that, batched over all hypotheses (numpy's stacked svd/qr/det call
-LAPACK once per matrix, so each hypothesis equals the reference's per-sample result)."""
+"""Host side of PnP RANSAC: mirrors PnPRANSAC.py:6-89 and LinearPnP.py:3-96 (names, argument meaning, return order,
+error behaviour) and drives the device kernels through the C ABI: K6a LinearPnP hypotheses (csrc/linpnp.cu), K6
+consensus scoring, K3 first-maximum argmax. Nothing here calls LAPACK: the reference's library conventions that its
+4-point hypotheses depend on (numpy's Vt[-1] of a rank-deficient DLT system, the Householder signs of qr) are replayed
+on the device -- see csrc/linpnp_math.cuh for what is pinned and for the one branch that cannot be (flag bit 0)."""
 from __future__ import annotations
 
 import numpy as np
@@ -13,84 +10,71 @@ import torch
 
 from . import _lib, device, sampler
 
+FLAG_REFLECTED = 1      # LinearPnP.py:88-90 branch: the reference's output there is decided by rounding noise
+FLAG_NONFINITE = 2
 
-def linear_pnp_batch(Xs, xs, K):
-    """LinearPnP.py:3-96 for a stack of problems. Xs [H,m,3], xs [H,m,2] -> (C [H,3], R [H,3,3])."""
-    Xs, xs, K = np.asarray(Xs, float), np.asarray(xs, float), np.asarray(K, float)
-    H, m = Xs.shape[0], Xs.shape[1]
-    if m < 4:
-        raise ValueError("At least 4 point correspondences are required for PnP")
-    Kinv = np.linalg.inv(K)
-    x_hom = np.concatenate([xs, np.ones((H, m, 1))], axis=2)
-    xn = np.einsum("ij,hmj->hmi", Kinv, x_hom)                       # :36-38
-    Xh = np.concatenate([Xs, np.ones((H, m, 1))], axis=2)
-    A = np.zeros((H, 2 * m, 12))
-    A[:, 0::2, 0:4] = Xh
-    A[:, 0::2, 8:12] = -xn[:, :, 0:1] * Xh
-    A[:, 1::2, 4:8] = Xh
-    A[:, 1::2, 8:12] = -xn[:, :, 1:2] * Xh                           # :45-53
-    _, _, Vt = np.linalg.svd(A)                                      # :56
-    P = Vt[:, -1, :].reshape(H, 3, 4)
-    M, t = P[:, :, :3].copy(), P[:, :, 3].copy()
-    neg = np.linalg.det(M) < 0                                       # :65-67
-    M[neg] *= -1
-    t[neg] *= -1
-    Q, Rqr = np.linalg.qr(np.transpose(M, (0, 2, 1)))                # :73
-    R = np.transpose(Q, (0, 2, 1))
-    scale = np.mean(np.diagonal(Rqr, axis1=1, axis2=2), axis=1)      # diag(Rqr.T) == diag(Rqr)
-    flip = scale < 0
-    R[flip] *= -1
-    scale = np.where(flip, -scale, scale)
-    U, _, Vt2 = np.linalg.svd(R)                                     # :84
-    R = U @ Vt2
-    bad = np.linalg.det(R) < 0
-    if np.any(bad):
-        U[bad, :, -1] *= -1
-        R[bad] = U[bad] @ Vt2[bad]
-    C_ = -np.einsum("hji,hj->hi", R, t / scale[:, None])             # :93-94
-    return C_, R
+
+def _hk(K):
+    K = np.ascontiguousarray(K, np.float64).reshape(3, 3)
+    return K, np.ascontiguousarray(np.linalg.inv(K))        # LinearPnP.py:38 normalises with numpy's inverse
+
+
+def linear_pnp4_device(d_X, d_x, d_samples, K, d_offsets=None, n_regs=1, want_pose=True, mute_reflected=True):
+    """K6a on device tensors: d_samples [n_regs * h, 4] i32 -> (d_C [H,3], d_R [H,9], d_P [H,12], d_flag [H] u8).
+    mute_reflected (the drop-in's policy): hypotheses of the noise-decided branch get a NaN row in d_P and cannot win
+    the consensus, as in the reference they all but never do (include/sfm_b200.h)."""
+    lib = _lib.load()
+    K, Kinv = _hk(K)
+    H = int(d_samples.shape[0])
+    d_P = device.empty((H, 12), torch.float64)
+    d_C = device.empty((H, 3), torch.float64) if want_pose else None
+    d_R = device.empty((H, 9), torch.float64) if want_pose else None
+    d_flag = device.empty((H,), torch.uint8)
+    n = int(d_X.shape[0]) if d_offsets is None else 0
+    _lib.check(lib.sfm_linear_pnp4_batch(device.ptr(d_X), device.ptr(d_x), device.ptr(d_offsets), int(n_regs), n,
+                                         device.ptr(d_samples), H // int(n_regs), K.ctypes.data, Kinv.ctypes.data,
+                                         1 if mute_reflected else 0, device.ptr(d_C), device.ptr(d_R), device.ptr(d_P), device.ptr(d_flag),
+                                         device.stream()), "sfm_linear_pnp4_batch")
+    return d_C, d_R, d_P, d_flag
+
+
+def linear_pnp_device(d_X, d_x, K):
+    """LinearPnP on ALL correspondences of one registration (device tensors) -> (d_CR [12], d_flag [1])."""
+    lib = _lib.load()
+    K, Kinv = _hk(K)
+    n = int(d_X.shape[0])
+    nbytes = int(lib.sfm_linear_pnp_npt_workspace_bytes(n))
+    ws = device.empty((nbytes,), torch.uint8)
+    d_CR = device.empty((12,), torch.float64)
+    d_flag = device.empty((1,), torch.uint8)
+    _lib.check(lib.sfm_linear_pnp_npt(device.ptr(d_X), device.ptr(d_x), n, K.ctypes.data, Kinv.ctypes.data,
+                                      device.ptr(d_CR), None, device.ptr(d_flag), device.ptr(ws), nbytes,
+                                      device.stream()), "sfm_linear_pnp_npt")
+    return d_CR, d_flag
 
 
 def LinearPnP(Xset, xset, K):
-    """LinearPnP.py:3-96 for one problem (any N >= 4)."""
-    Xset, xset = np.array(Xset), np.array(xset)
-    if len(Xset) < 4:
+    """Drop-in for LinearPnP.py:3-96 -> (C (3,), R (3,3))."""
+    Xset, xset, K = np.array(Xset), np.array(xset), np.array(K)
+    if len(Xset) < 4:                                                # :31-32
         raise ValueError("At least 4 point correspondences are required for PnP")
-    C_, R = linear_pnp_batch(Xset[None], xset[None], K)
-    return C_[0], R[0]
+    d_CR, _ = linear_pnp_device(device.to_device(Xset.astype(np.float64)), device.to_device(xset.astype(np.float64)), K)
+    cr = d_CR.cpu().numpy()
+    return cr[:3].copy(), cr[3:].reshape(3, 3).copy()
 
 
-def pnp_score_device(d_P, d_X, d_x, threshold):
+def pnp_score_device(d_P, d_X, d_x, threshold, d_counts=None, d_best=None):
     """K6 + K3 on device tensors -> (d_counts [h] i32, d_best [2] i32)."""
     lib = _lib.load()
     h, n = int(d_P.shape[0]), int(d_X.shape[0])
-    d_counts = device.empty((h,), torch.int32)
-    d_best = device.empty((2,), torch.int32)
+    d_counts = device.empty((h,), torch.int32) if d_counts is None else d_counts
+    d_best = device.empty((2,), torch.int32) if d_best is None else d_best
     st = device.stream()
     _lib.check(lib.sfm_pnp_score_count(device.ptr(d_P), device.ptr(d_X), device.ptr(d_x), n, h,
                                        float(threshold), device.ptr(d_counts), st), "sfm_pnp_score_count")
     _lib.check(lib.sfm_argmax_first(device.ptr(d_counts), h, 0, device.ptr(d_best), None, st),
                "sfm_argmax_first")
     return d_counts, d_best
-
-
-def pnp_hypotheses(X, x, K, samples):
-    """Poses of every sampled 4-tuple; a failing LAPACK call marks only that hypothesis invalid
-    (the reference's per-iteration try/except, PnPRANSAC.py:53,77-79)."""
-    with np.errstate(all="ignore"):
-        try:
-            C_, R = linear_pnp_batch(X[samples], x[samples], K)
-        except np.linalg.LinAlgError:
-            H = len(samples)
-            C_, R = np.full((H, 3), np.nan), np.full((H, 3, 3), np.nan)
-            for i, s in enumerate(samples):
-                try:
-                    C_[i], R[i] = LinearPnP(X[s], x[s], K)
-                except Exception:
-                    pass
-        t = -np.einsum("hij,hj->hi", R, C_)
-        P = np.einsum("ij,hjk->hik", K, np.concatenate([R, t[:, :, None]], axis=2))   # :60
-    return C_, R, np.ascontiguousarray(P.reshape(len(samples), 12))
 
 
 def PnPRANSAC(X, x, K, threshold=200, n_max=1000, info=None):
@@ -103,22 +87,60 @@ def PnPRANSAC(X, x, K, threshold=200, n_max=1000, info=None):
         raise ValueError("At least 4 point correspondences are required for PnP")
     best_C = best_R = None
     best_count = 0
+    d_X, d_x = device.to_device(X.astype(np.float64)), device.to_device(x.astype(np.float64))
     if n_max > 0:
         samples = sampler.sample_stream(n_points, 4, int(n_max))     # one draw per iteration (:49)
-        Xf, xf = X.astype(np.float64), x.astype(np.float64)
-        C_, R, P = pnp_hypotheses(Xf, xf, K.astype(np.float64), samples)
-        d_counts, d_best = pnp_score_device(device.to_device(P), device.to_device(Xf),
-                                            device.to_device(xf), threshold)
-        best = d_best.cpu().numpy()
-        best_count = int(best[1])
-        if best_count > 0:
-            best_C, best_R = C_[best[0]].copy(), R[best[0]].copy()
+        d_C, d_R, d_P, d_flag = linear_pnp4_device(d_X, d_x, device.to_device(samples, np.int32), K)
+        d_counts, d_best = pnp_score_device(d_P, d_X, d_x, threshold)
+        w = d_best[:1].long()
+        # one D2H: (winner index, count) | C | R of the winner
+        packed = torch.cat([d_best.double(), d_C.index_select(0, w).reshape(-1), d_R.index_select(0, w).reshape(-1)])
+        packed = packed.cpu().numpy()
+        best_count = int(packed[1])
+        if best_count > 0:                                           # strict '>' from zero (:72): count 0 never wins
+            best_C, best_R = packed[2:5].copy(), packed[5:14].reshape(3, 3).copy()
         if info is not None:
-            info.update(best_idx=int(best[0]), best_count=best_count, counts=d_counts.cpu().numpy(), P=P)
+            info.update(best_idx=int(packed[0]), best_count=best_count, counts=d_counts.cpu().numpy(),
+                        P=d_P.cpu().numpy(), flags=d_flag.cpu().numpy(), samples=samples)
     if best_C is None or best_count < 4:                             # :82-87
         try:
-            best_C, best_R = LinearPnP(X, x, K)
+            cr = linear_pnp_device(d_X, d_x, K)[0].cpu().numpy()
+            best_C, best_R = cr[:3].copy(), cr[3:].reshape(3, 3).copy()
             print("Warning: PnP RANSAC failed, using linear PnP on all points")
         except Exception as e:
             raise ValueError(f"PnP estimation failed: {e}")
     return best_C, best_R
+
+
+def pnp_ransac_batch(X_list, x_list, K, threshold=200, n_max=1000):
+    """Many registrations at once (BASELINE config 4: 500 x 2,000 correspondences x 1,000 hypotheses): the sample
+    streams are drawn registration after registration from the global `random` stream exactly as consecutive
+    PnPRANSAC calls would, ONE hypothesis launch covers all registrations, scoring + argmax run per registration on
+    slices, one D2H brings all winners back. Returns (C [B,3], R [B,3,3], counts [B]). Registrations whose best
+    count is below 4 fall back to LinearPnP on all their points (PnPRANSAC.py:82-87)."""
+    B = len(X_list)
+    sizes = [len(X) for X in X_list]
+    if min(sizes) < 4:
+        raise ValueError("At least 4 point correspondences are required for PnP")
+    offs = np.zeros(B + 1, np.int32)
+    offs[1:] = np.cumsum(sizes)
+    samples = np.empty((B * n_max, 4), np.int32)
+    for b in range(B):
+        sampler.sample_stream(sizes[b], 4, int(n_max), out=samples[b * n_max:(b + 1) * n_max])
+    d_X = device.to_device(np.concatenate([np.asarray(X, np.float64) for X in X_list]))
+    d_x = device.to_device(np.concatenate([np.asarray(x, np.float64) for x in x_list]))
+    d_off = device.to_device(offs, np.int32)
+    d_C, d_R, d_P, _ = linear_pnp4_device(d_X, d_x, device.to_device(samples, np.int32), K, d_off, B)
+    d_counts = device.empty((B * n_max,), torch.int32)
+    d_best = device.empty((B, 2), torch.int32)
+    for b in range(B):
+        pnp_score_device(d_P[b * n_max:(b + 1) * n_max], d_X[offs[b]:offs[b + 1]], d_x[offs[b]:offs[b + 1]], threshold,
+                         d_counts[b * n_max:(b + 1) * n_max], d_best[b])
+    w = d_best[:, 0].long() + torch.arange(B, device=d_best.device) * n_max
+    packed = torch.cat([d_best[:, 1:2].double(), d_C.index_select(0, w), d_R.index_select(0, w)], dim=1).cpu().numpy()
+    counts = packed[:, 0].astype(np.int64)
+    C_, R_ = packed[:, 1:4].copy(), packed[:, 4:13].reshape(B, 3, 3).copy()
+    for b in np.nonzero(counts < 4)[0]:
+        cr = linear_pnp_device(d_X[offs[b]:offs[b + 1]], d_x[offs[b]:offs[b + 1]], K)[0].cpu().numpy()
+        C_[b], R_[b] = cr[:3], cr[3:].reshape(3, 3)
+    return C_, R_, counts
