@@ -80,6 +80,45 @@ def _timed(ns, wf, fx, fy, flag, K):
     return time.perf_counter() - t, log
 
 
+def run_p3data(seed: int = 0, runs: int = 3) -> dict | None:
+    """BASELINE configs[0] itself: the UNMODIFIED Wrapper_dev.sfm_wrapper on P3Data at the wrapper's own settings
+    (F threshold 0.06 px, 1000 hypotheses), once as shipped (reference CPU code from oracle/_ref) and once with the
+    drop-in directory ahead of it on sys.path. Drawing is stubbed in both; Utils.get_data (text parsing, reference
+    code) is inside both timings. None when oracle/_ref did not travel."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    try:
+        import wrapper_harness as wh
+    finally:
+        sys.path.pop(0)
+    if not wh.available():
+        return None
+    wh.run(True, seed)                                              # warm
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(runs):
+        t = time.perf_counter()
+        got, _ = wh.run(True, seed)
+        torch.cuda.synchronize()
+        ts.append(time.perf_counter() - t)
+    t = time.perf_counter()
+    ref, _ = wh.run(False, seed)
+    t_ref = time.perf_counter() - t
+    same = all(np.array_equal(np.asarray(a[2][1]), np.asarray(b[2][1]))
+               for a, b in zip(got["get_inliers_ransac"], ref["get_inliers_ransac"]))
+    Xg, Xr = got["nonlinear_triangulation"][0][2], ref["nonlinear_triangulation"][0][2]
+    return {"workload": "C1: unmodified Wrapper_dev.sfm_wrapper on P3Data (5 images, 10 pairs: homography RANSAC 30 px / "
+                        "1000 + F RANSAC 0.06 px / 1000 per pair, two-view pose, linear + non-linear triangulation of "
+                        f"{len(Xr)} points; PnP and bundle adjustment are not reached on this data), seed {seed}",
+            "api": "dropin/ ahead of the reference on sys.path; nothing else changes",
+            "seconds": float(np.mean(ts)), "seconds_min": float(min(ts)), "runs": runs,
+            "cpu_baseline": {"seconds": t_ref, "cores": 1, "kind": "reference",
+                             "sample": "the same call as shipped, one run"},
+            "speedup_vs_reference": t_ref / float(np.mean(ts)),
+            "parity": {"f_inlier_sets_equal_all_pairs": bool(same), "rng_state_equal": got["rng_after"] == ref["rng_after"],
+                       "refined_points_rel_err": float(np.linalg.norm(Xg - Xr) / np.linalg.norm(Xr))}}
+
+
 def run(with_cpu: bool = True) -> dict:
     import torch
     wf = _flow()
@@ -105,6 +144,9 @@ def run(with_cpu: bool = True) -> dict:
                                "sample": "the same flow, one run, oracle port of the reference (numpy/scipy)",
                                "same_inlier_sets_and_registrations": same}
         out["speedup_vs_cpu_port"] = dt / out["seconds"]
+        p3 = run_p3data()
+        if p3 is not None:
+            out["p3data"] = p3
     return out
 
 

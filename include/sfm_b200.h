@@ -337,6 +337,16 @@ int sfm_linear_pnp_npt(const double *d_X, const double *d_x, int32_t n, const do
                        const double *h_Kinv, double *d_CR, double *d_P, uint8_t *d_flag, void *d_ws,
                        size_t ws_bytes, void *stream);
 
+/* ---- a3 / a5: the residual functions the reference exports next to its solvers -----------------------
+ * sfm_tri_residuals: Loss(X, x1, x2, P1, P2) of NonLinearTriangulation.py:5-50 for n points:
+ *   d_r [n,4] = [x1 - pi(P1 X~), x2 - pi(P2 X~)], pi = exact division, a view with |w| < 1e-8 gives 0.
+ * sfm_pnp_residuals: NonLinearPnPLoss(X0, X, x, K) of NonlinearPnP.py:5-44: h_rt HOST [6] = (rotvec, t),
+ *   d_r [2n] interleaved [du, dv] = x - a[:2] / (a[2] + 1e-8). h_P1, h_P2 [12], h_K [9]: HOST. */
+int sfm_tri_residuals(const double *h_P1, const double *h_P2, const double *d_x1, const double *d_x2,
+                      const double *d_X, int32_t n, double *d_r, void *stream);
+int sfm_pnp_residuals(const double *h_K, const double *h_rt, const double *d_X, const double *d_x, int32_t n,
+                      double *d_r, void *stream);
+
 /* @@MORE@@ (further sections are appended above this marker as the path widens) */
 
 /* ---- N4: two-view pose front end ------------------------------------------------

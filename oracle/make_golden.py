@@ -231,6 +231,46 @@ def gen_linpnp():
     save("linpnp4.npz", K=scenes.K_REF, **out)
 
 
+def gen_wrapper():
+    """BASELINE config 1 as the reference runs it: the UNMODIFIED Wrapper_dev.sfm_wrapper on P3Data (drawing
+    stubbed), seeds 0..5, every hot call recorded through the names the wrapper bound (tests/wrapper_harness.py).
+    Per pair: homography + inlier index set, F + inlier index set; for pair 1_2: E, the four poses, the chosen pose,
+    linear and refined points. PnP / BA are not reached on this data (14-18 points survive)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import wrapper_harness as wh
+    assert wh.available()
+    out = {}
+    for seed in range(6):
+        log, _ = wh.run(False, seed)
+        pre = f"s{seed}_"
+        if seed == 0:
+            fx, fy, fl = log["get_data"][0][2]
+            out.update(feature_x=fx, feature_y=fy, feature_flag=fl)
+        out[pre + "n_pairs"] = len(log["get_homography_inliers"])
+        for k, c in enumerate(log["get_homography_inliers"]):
+            H, idx = c[2]
+            out[pre + f"H_{k}"] = np.full((3, 3), np.nan) if H is None else H
+            out[pre + f"hidx_{k}"] = np.asarray(idx, np.int64)
+        out[pre + "n_f"] = len(log["get_inliers_ransac"])
+        for k, c in enumerate(log["get_inliers_ransac"]):
+            F, idx = c[2]
+            out[pre + f"F_{k}"] = np.full((3, 3), np.nan) if F is None else F
+            out[pre + f"fidx_{k}"] = np.asarray(idx, np.int64)
+        out[pre + "E"] = log["EssentialMatrixFromFundamentalMatrix"][0][2]
+        Cset, Rset = log["ExtractCameraPose"][0][2]
+        out[pre + "Cset"], out[pre + "Rset"] = np.array(Cset), np.array(Rset)
+        Cc, Rc = log["get_correct_camera_pose"][0][2]
+        out[pre + "C_corr"], out[pre + "R_corr"] = np.array(Cc), np.array(Rc)
+        lt = log["linear_triangulation"]
+        out[pre + "X_candidates"] = np.array([c[2] for c in lt[:4]])
+        out[pre + "X_linear"] = lt[4][2]
+        out[pre + "X_refined"] = log["nonlinear_triangulation"][0][2]
+        out[pre + "calls"] = np.array([len(log[n]) for n in wh.HOT], np.int64)
+        out[pre + "rng_after"] = log["rng_after"]
+        print(seed, "F inliers per pair", [len(c[2][1]) for c in log["get_inliers_ransac"]], "points", len(out[pre + "X_refined"]))
+    save("p3data_wrapper.npz", **out)
+
+
 def dense_ba_inputs(sc, n_extra=7):
     """Dense (F x n_img) arrays in the shape perform_bundle_adjustment takes, with some
     untriangulated filler rows so that the valid-point remapping is exercised."""
@@ -284,6 +324,6 @@ def gen_ba():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["f8pt", "fransac", "p3data", "tri", "pnp", "linpnp", "ba", "twoview", "homography"]
+    which = sys.argv[1:] or ["f8pt", "fransac", "p3data", "tri", "pnp", "linpnp", "ba", "twoview", "homography", "wrapper"]
     for w in which:
         globals()["gen_" + w]()

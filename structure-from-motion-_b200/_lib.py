@@ -65,6 +65,8 @@ SIGNATURES = {
     "sfm_linear_pnp_npt_workspace_bytes": (C.c_size_t, [C.c_int32]),
     "sfm_linear_pnp_npt": (C.c_int, [c_f64p, c_f64p, C.c_int32, c_vp, c_vp, c_f64p, c_f64p, c_u8p, c_vp, C.c_size_t,
                                      c_vp]),
+    "sfm_tri_residuals": (C.c_int, [c_vp, c_vp, c_f64p, c_f64p, c_f64p, C.c_int32, c_f64p, c_vp]),
+    "sfm_pnp_residuals": (C.c_int, [c_vp, c_vp, c_f64p, c_f64p, C.c_int32, c_f64p, c_vp]),
     "sfm_ba_default_options": (None, [c_vp]),
     "sfm_ba_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "sfm_ba_last_profile": (C.c_int, [c_vp]),

@@ -63,16 +63,22 @@ def linear_triangulation(K, C1, R1, C2, R2, x1, x2):
 # ---------------------------------------------------------------------------------------------
 # NonLinearTriangulation.py
 # ---------------------------------------------------------------------------------------------
+def tri_residuals_device(P1, P2, d_x1, d_x2, d_X):
+    """Loss() for n points on device tensors -> d_r [n,4] (sfm_tri_residuals)."""
+    n = int(d_X.shape[0])
+    d_r = device.empty((n, 4), torch.float64)
+    P1, P2 = np.ascontiguousarray(P1, np.float64), np.ascontiguousarray(P2, np.float64)
+    _lib.check(_lib.load().sfm_tri_residuals(_hptr(P1), _hptr(P2), device.ptr(d_x1), device.ptr(d_x2), device.ptr(d_X), n,
+                                             device.ptr(d_r), device.stream()), "sfm_tri_residuals")
+    return d_r
+
+
 def Loss(X, x1, x2, P1, P2):
-    """NonLinearTriangulation.py:5-50 (exported name; a 4-number convenience, the kernels
-    evaluate the same residual internally)."""
-    X_hom = np.array([X[0], X[1], X[2], 1])
-    out = []
-    for P, x in ((P1, x1), (P2, x2)):
-        v = P @ X_hom
-        proj = np.array([x[0], x[1]]) if abs(v[2]) < 1e-8 else v[:2] / v[2]
-        out.append(x - proj)
-    return np.hstack(out)
+    """Drop-in for NonLinearTriangulation.py:5-50 -> residual (4,): one point through sfm_tri_residuals."""
+    X, x1, x2 = np.asarray(X, np.float64), np.asarray(x1, np.float64), np.asarray(x2, np.float64)
+    d_r = tri_residuals_device(P1, P2, device.to_device(x1.reshape(1, 2)), device.to_device(x2.reshape(1, 2)),
+                               device.to_device(X.reshape(1, 3)))
+    return d_r.cpu().numpy().reshape(4)
 
 
 def nltri_device(P1, P2, d_x1, d_x2, d_X0, max_nfev=TRI_MAX_NFEV, tol=REF_TOL, want_info=False):
@@ -118,13 +124,22 @@ def nonlinear_triangulation(K, C1, R1, C2, R2, x1, x2, x0):
 # ---------------------------------------------------------------------------------------------
 # NonlinearPnP.py
 # ---------------------------------------------------------------------------------------------
+def pnp_residuals_device(K, rt, d_X, d_x):
+    """NonLinearPnPLoss() on device tensors -> d_r [2n] interleaved (sfm_pnp_residuals)."""
+    n = int(d_X.shape[0])
+    d_r = device.empty((2 * n,), torch.float64)
+    K, rt = np.ascontiguousarray(K, np.float64), np.ascontiguousarray(rt, np.float64)
+    _lib.check(_lib.load().sfm_pnp_residuals(_hptr(K), _hptr(rt), device.ptr(d_X), device.ptr(d_x), n, device.ptr(d_r),
+                                             device.stream()), "sfm_pnp_residuals")
+    return d_r
+
+
 def NonLinearPnPLoss(X0, X, x, K):
-    """NonlinearPnP.py:5-44 (exported name)."""
-    R = Rotation.from_rotvec(X0[:3]).as_matrix()
-    C_ = -R.T @ X0[3:6]
-    P = K @ np.hstack([R, -R @ C_.reshape(3, 1)])
-    ph = (P @ np.hstack([X, np.ones((X.shape[0], 1))]).T).T
-    return (x - ph[:, :2] / (ph[:, 2:3] + 1e-8)).flatten()
+    """Drop-in for NonlinearPnP.py:5-44 -> residual (2N,), interleaved [du, dv]."""
+    X, x = np.asarray(X, np.float64), np.asarray(x, np.float64)
+    if len(X) == 0:
+        return np.zeros(0)
+    return pnp_residuals_device(K, np.asarray(X0, np.float64)[:6], device.to_device(X), device.to_device(x)).cpu().numpy()
 
 
 def nlpnp_batch_device(K, d_X, d_x, d_offsets, d_rt0, max_nfev=PNP_MAX_NFEV, tol=REF_TOL):

@@ -143,3 +143,45 @@ def test_lintri_golden_and_dropin(cuda_device):
     # the pipeline composition the wrapper uses (Wrapper_dev.py:179,187): x0 -> non-linear refinement
     Xr = refine.NonLinearTriangulation(g["K"], g["C1"], g["R1"], g["C2"], g["R2"], g["x1"], g["x2"], X)
     assert rel_err(Xr, g["X"]) < 1e-6
+
+
+def test_tri_loss_matches_reference_residuals(cuda_device):
+    """a3: Loss() (NonLinearTriangulation.py:5-50) as sfm_tri_residuals against the reference's own residual vectors
+    (golden loss0 = Loss at x0 for 300 points), through the exported drop-in name, and tied to K5: the cost K5
+    reports at its solution is 0.5 |Loss|^2 of the residual kernel there."""
+    from sfm_b200 import device, refine
+    g = golden("nltri.npz")
+    P1, P2 = so.projection_matrix(g["K"], g["C1"], g["R1"]), so.projection_matrix(g["K"], g["C2"], g["R2"])
+    d_x1, d_x2, d_X0 = device.to_device(g["x1"]), device.to_device(g["x2"]), device.to_device(g["x0"])
+    r = refine.tri_residuals_device(P1, P2, d_x1, d_x2, d_X0).cpu().numpy()
+    assert r.shape == g["loss0"].shape and np.max(np.abs(r - g["loss0"])) < 1e-9
+    for i in (0, 17, 299):
+        assert np.max(np.abs(refine.Loss(g["x0"][i], g["x1"][i], g["x2"][i], P1, P2) - g["loss0"][i])) < 1e-9
+    d_X, d_cost, _ = refine.nltri_device(P1, P2, d_x1, d_x2, d_X0, want_info=True)
+    rs = refine.tri_residuals_device(P1, P2, d_x1, d_x2, d_X).cpu().numpy()
+    assert np.allclose(d_cost.cpu().numpy(), 0.5 * np.sum(rs ** 2, axis=1), rtol=1e-12, atol=1e-15)
+    # a view whose depth vanishes contributes a zero residual (:33-34, :40-41)
+    Xdeg = np.array([[0.0, 0.0, 0.0]]) + g["C1"]               # the first camera's centre: w = 0 in view 1
+    rd = refine.tri_residuals_device(P1, P2, device.to_device(g["x1"][:1]), device.to_device(g["x2"][:1]),
+                                     device.to_device(Xdeg)).cpu().numpy()[0]
+    assert rd[0] == 0.0 and rd[1] == 0.0 and np.all(np.isfinite(rd))
+    assert np.allclose(rd, so.tri_loss(Xdeg[0], g["x1"][0], g["x2"][0], P1, P2), atol=1e-9)
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+def test_pnp_loss_matches_reference_residuals(cuda_device, tag):
+    """a5: NonLinearPnPLoss (NonlinearPnP.py:5-44) as sfm_pnp_residuals against golden loss0_* (the reference's
+    residual at the initial pose), through the exported name, and tied to K7's reported cost."""
+    from sfm_b200 import device, refine
+    g = golden("pnp.npz")
+    X, x, K = g[f"X_{tag}"], g[f"x_{tag}"], g["K"]
+    rt0 = so.pose_to_params(g[f"C0_{tag}"], g[f"R0_{tag}"])
+    r = refine.NonLinearPnPLoss(rt0, X, x, K)
+    ref = g[f"loss0_{tag}"]
+    assert r.shape == ref.shape and np.max(np.abs(r - ref)) <= 1e-9 * max(1.0, np.max(np.abs(ref)))
+    d_X, d_x = device.to_device(X), device.to_device(x)
+    d_off = device.to_device(np.array([0, len(X)], np.int32), np.int32)
+    d_rt, d_cost, _ = refine.nlpnp_batch_device(K, d_X, d_x, d_off, device.to_device(rt0.reshape(1, 6)))
+    rs = refine.pnp_residuals_device(K, d_rt.cpu().numpy()[0], d_X, d_x).cpu().numpy()
+    assert np.isclose(float(d_cost.cpu()[0]), 0.5 * float(rs @ rs), rtol=1e-11)
+    assert refine.NonLinearPnPLoss(rt0, X[:0], x[:0], K).shape == (0,)
