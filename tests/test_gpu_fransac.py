@@ -115,6 +115,36 @@ def test_fransac_full_size_properties(cuda_device):
     assert np.array_equal(r3.counts.cpu().numpy(), counts)
 
 
+def test_fransac_c2_full_size_against_the_oracle(cuda_device, tmp_path):
+    """Parity AT THE BENCHMARK SIZE (BASELINE configs[1]: 50k correspondences, 30 % outliers, 100k hypotheses,
+    threshold 0.06): the oracle scores the whole stream on all host cores (tests/oracle_pool.py, a process of its
+    own) and every one of the 100,000 per-hypothesis counts, the winner, its F and its inlier mask are compared with
+    the GPU's -- masks bit-exact outside a 1e-9 band around the threshold (band population reported)."""
+    import oracle_pool
+    from sfm_b200 import sampler
+    from oracle import scenes
+    ransac = _ransac()
+    sc = scenes.two_view()
+    random.seed(12345)
+    samples = sampler.sample_stream(50_000, 8, 100_000)
+    got = ransac.f_ransac_host(sc["x1"], sc["x2"], samples, 0.06, want_all=True)
+    ref = oracle_pool.run(sc["x1"], sc["x2"], samples, 0.06, str(tmp_path))
+    mism = np.nonzero(got["counts"] != ref["counts"])[0]
+    for k in mism:                                        # a count may only differ through points in the band
+        e = so.f_errors(ref["F"][k].reshape(3, 3), sc["x1"], sc["x2"])
+        assert abs(int(got["counts"][k]) - int(ref["counts"][k])) <= int((np.abs(e - 0.06) < 1e-9).sum()), k
+    assert len(mism) <= 10, len(mism)
+    assert got["best_idx"] == int(ref["best_idx"]) and got["best_count"] == int(ref["best_count"])
+    band = np.abs(ref["err"] - 0.06) < 1e-9
+    assert np.array_equal(got["mask"][~band], ref["mask"][~band])
+    assert rel_err(got["F_best"].ravel(), ref["F"][got["best_idx"]]) < 1e-6
+    scoring = ref["counts"] > 0
+    rel = np.linalg.norm(got["F"] - ref["F"], axis=1) / np.linalg.norm(ref["F"], axis=1)
+    assert np.nanmax(rel[scoring]) < 1e-6
+    print(f"C2 full size: {len(mism)} count mismatches of 100000, band population {int(band.sum())}, winner "
+          f"{got['best_idx']} ({got['best_count']} inliers), max rel F over scoring hypotheses {np.nanmax(rel[scoring]):.2e}")
+
+
 def test_estimate_fundamental_matrix(cuda_device):
     g = golden("f8pt.npz")
     ransac = _ransac()

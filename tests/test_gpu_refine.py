@@ -185,3 +185,30 @@ def test_pnp_loss_matches_reference_residuals(cuda_device, tag):
     rs = refine.pnp_residuals_device(K, d_rt.cpu().numpy()[0], d_X, d_x).cpu().numpy()
     assert np.isclose(float(d_cost.cpu()[0]), 0.5 * float(rs @ rs), rtol=1e-11)
     assert refine.NonLinearPnPLoss(rt0, X[:0], x[:0], K).shape == (0,)
+
+
+def test_c4_million_points_against_the_oracle_on_a_subset(cuda_device):
+    """Parity AT THE BENCHMARK SIZE (BASELINE configs[3]): LinearTriangulation + NonLinearTriangulation over
+    1,000,000 points of the C4 two-view scene in one call each; a random 2,000-point subset is refined by the oracle
+    (scipy least_squares 'lm' per point, NonLinearTriangulation.py:116-122) from the same linear start and compared:
+    linear points 1e-9, refined points and their per-point cost 1e-6 relative."""
+    from oracle import scenes
+    from sfm_b200 import device, refine
+    n = 1_000_000
+    sc = scenes.two_view(n=n, outlier_frac=0.0, noise=0.5, seed=20260104)
+    P1 = refine.projection_matrix(sc["K"], sc["C1"], sc["R1"])
+    P2 = refine.projection_matrix(sc["K"], sc["C2"], sc["R2"])
+    d_x1, d_x2 = device.to_device(sc["x1"]), device.to_device(sc["x2"])
+    d_X0 = refine.lintri_device(P1, P2, d_x1, d_x2)
+    d_X, d_cost, d_st = refine.nltri_device(P1, P2, d_x1, d_x2, d_X0, want_info=True)
+    X0, X, st = d_X0.cpu().numpy(), d_X.cpu().numpy(), d_st.cpu().numpy()
+    assert np.all((st >> 16) > 0) and np.all(np.isfinite(X))
+    idx = np.random.default_rng(1).choice(n, 2000, replace=False)
+    cam = (sc["K"], sc["C1"], sc["R1"], sc["C2"], sc["R2"])
+    X0o = so.linear_triangulation(*cam, sc["x1"][idx], sc["x2"][idx])
+    assert np.max(np.linalg.norm(X0[idx] - X0o, axis=1) / np.linalg.norm(X0o, axis=1)) < 1e-9
+    Xo = so.nonlinear_triangulation(*cam, sc["x1"][idx], sc["x2"][idx], X0o)
+    assert np.max(np.linalg.norm(X[idx] - Xo, axis=1) / np.linalg.norm(Xo, axis=1)) < 1e-6
+    c_g, c_o = so.tri_cost(*cam, sc["x1"][idx], sc["x2"][idx], X[idx]), so.tri_cost(*cam, sc["x1"][idx], sc["x2"][idx], Xo)
+    assert np.all(np.abs(c_g - c_o) <= 1e-6 * np.maximum(c_o, 1e-12) + 1e-12)
+    assert np.allclose(d_cost.cpu().numpy()[idx], c_g, rtol=1e-9, atol=1e-12)
