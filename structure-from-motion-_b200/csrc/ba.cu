@@ -46,6 +46,7 @@ struct CholDagPlan;
 CholDagPlan *chol_dag_create(const uint8_t *h_pattern, int nb, int order_mode, cudaStream_t st, int *rc);
 int chol_dag_launch(CholDagPlan *p, const double *A, size_t ld, int npad, double *d_x, int *d_fail, cudaStream_t st);
 void chol_dag_destroy(CholDagPlan *p, cudaStream_t st);
+int chol_dag_zero_system(CholDagPlan *p, double *A, size_t ld, cudaStream_t st);
 constexpr int BA_NB = 48;                 // == CH_NB in chol.cu
 constexpr int BA_CHUNK = 2048;            // observations per camera-pass CTA
 constexpr int K9P_WARP_SCRATCH = 9 * 33 + 18;   // doubles of shared memory per warp of K9p (T[9][33] + 34 ints, padded)
@@ -704,18 +705,25 @@ __global__ void ba_pair_emit_kernel(const int32_t *__restrict__ pt_ptr, const in
     }
 }
 
-// Z [nobs,18] as an array of records (the gather reads whole records at random). Thread per
-// observation, W planes read coalesced; the 32 records of a warp are contiguous in Z, so they go
-// through shared memory and leave as 288 consecutive 16-byte words (whole sectors: scattered
-// half-sector stores made L2 fetch every line from DRAM before merging).
+// Z as an array of records the gather reads whole, at random. A record is Z_o (6 x 3 = 18 doubles) padded to 20
+// doubles = 160 bytes = five whole 32-byte sectors, and it is stored at the CAMERA-MAJOR position zpos[o] of its
+// observation: the pair list is sorted by (hi camera, lo camera), so consecutive list entries walk through the
+// segments of two cameras -- a working set of a few hundred KB that stays in L2, where the point-major order this
+// replaced scattered every block's records over the whole 0.6 GB array (2.7 GB of DRAM traffic per gather at C5,
+// L2 hit rate 61 %). Thread per observation, W planes read coalesced; the 32 records of a warp go through shared
+// memory and leave three at a time, ten lanes per record, so every store instruction writes whole sectors
+// (scattered part-sector stores make L2 fetch the line from DRAM before merging).
+constexpr int ZREC = 10;                   // 16-byte words per record
 __global__ void __launch_bounds__(256)
 ba_schur_z_kernel(const double *__restrict__ W, int nobs, const int32_t *__restrict__ pt_idx,
-                  const double *__restrict__ Ginv, double *__restrict__ Z) {
+                  const int32_t *__restrict__ zpos, const double *__restrict__ Ginv, double *__restrict__ Z) {
     __shared__ __align__(16) double2 sz[8][288];
     const int o = blockIdx.x * 256 + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int zp = -1;
     if (o < nobs) {
         const int p = pt_idx[o];
+        zp = zpos[o];
         double g[6];
 #pragma unroll
         for (int i = 0; i < 6; ++i) g[i] = Ginv[6 * (size_t)p + i];
@@ -732,11 +740,20 @@ ba_schur_z_kernel(const double *__restrict__ W, int nobs, const int32_t *__restr
         for (int i = 0; i < 9; ++i) sz[warp][9 * lane + i] = make_double2(z[2 * i], z[2 * i + 1]);
     }
     __syncwarp();
-    const int o_w = o - lane;                                   // first observation of this warp
-    if (o_w >= nobs) return;
-    const int words = 9 * min(32, nobs - o_w);
-    double2 *dst = reinterpret_cast<double2 *>(Z) + 9 * (size_t)o_w;
-    for (int c = lane; c < words; c += 32) dst[c] = sz[warp][c];
+    double2 *Z2 = reinterpret_cast<double2 *>(Z);
+    const int sub = lane / ZREC, part = lane - ZREC * sub;          // lanes 0..29: record sub of this round, word part
+#pragma unroll
+    for (int rnd = 0; rnd < 11; ++rnd) {
+        const int rec = 3 * rnd + sub;
+        const int dst = __shfl_sync(0xffffffffu, zp, rec < 32 ? rec : 0);
+        if (lane < 3 * ZREC && rec < 32 && dst >= 0)
+            Z2[(size_t)ZREC * dst + part] = part < 9 ? sz[warp][9 * rec + part] : make_double2(0.0, 0.0);
+    }
+}
+
+__global__ void ba_invert_perm_kernel(const int32_t *__restrict__ perm, int n, int32_t *__restrict__ inv) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < n) inv[perm[c]] = c;
 }
 
 __device__ __forceinline__ void sg_flush(double *__restrict__ S, size_t ld, int nc, uint32_t key, double (&acc)[36],
@@ -765,15 +782,17 @@ __device__ __forceinline__ void sg_flush(double *__restrict__ S, size_t ld, int 
 // SG_DEAD as key and observation 0.
 constexpr uint32_t SG_DEAD = 0xFFFFFFFFu;
 __global__ void ba_pair_interleave_kernel(const uint32_t *__restrict__ keys, const uint2 *__restrict__ pairs,
-                                          size_t npairs, int seg, size_t npadded, uint32_t *__restrict__ keys_i,
-                                          uint2 *__restrict__ pairs_i) {
+                                          const int32_t *__restrict__ zpos, size_t npairs, int seg, size_t npadded,
+                                          uint32_t *__restrict__ keys_i, uint2 *__restrict__ pairs_i) {
     const size_t d = (size_t)blockIdx.x * blockDim.x + threadIdx.x;      // destination index
     if (d >= npadded) return;
     const size_t lane = d & 31, wi = d >> 5, w = wi / seg, it = wi - w * seg;
     const size_t src = (w * 32 + lane) * (size_t)seg + it;
     const bool ok = src < npairs;
     keys_i[d] = ok ? keys[src] : SG_DEAD;
-    pairs_i[d] = ok ? pairs[src] : make_uint2(0u, 0u);
+    // observation indices -> positions of their records in the camera-major Z array
+    const uint2 pr = ok ? pairs[src] : make_uint2(0u, 0u);
+    pairs_i[d] = ok ? make_uint2((unsigned)zpos[pr.x], (unsigned)zpos[pr.y]) : make_uint2(0u, 0u);
 }
 
 // Lane = one slice of `seg` consecutive entries of the sorted list. The two 144-byte records of
@@ -793,15 +812,15 @@ __device__ __forceinline__ void sg_fetch(double2 *__restrict__ dst, const double
         const int c = lane + 32 * rnd, src = c / 9, part = c - 9 * src;
         const unsigned oi = __shfl_sync(0xffffffffu, me.x, src), oj = __shfl_sync(0xffffffffu, me.y, src);
         const unsigned s0 = (unsigned)__cvta_generic_to_shared(dst + c), s1 = (unsigned)__cvta_generic_to_shared(dst + 288 + c);
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s0), "l"(Z2 + 9 * (size_t)oi + part));
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s1), "l"(Z2 + 9 * (size_t)oj + part));
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s0), "l"(Z2 + ZREC * (size_t)oi + part));
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s1), "l"(Z2 + ZREC * (size_t)oj + part));
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
 __global__ void __launch_bounds__(SG_THREADS, 3)
 ba_schur_gather_kernel(const uint32_t *__restrict__ keys, const uint2 *__restrict__ pairs, int seg,
-                       const double *__restrict__ Z, const int32_t *__restrict__ pt_idx, const double *__restrict__ H,
+                       const double *__restrict__ Z, const int32_t *__restrict__ pt_c, const double *__restrict__ H,
                        int nc, double *__restrict__ S, size_t ld, double *__restrict__ gred) {
     extern __shared__ __align__(16) double2 srec[];      // [warp][stage][2][288]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -847,7 +866,7 @@ ba_schur_gather_kernel(const uint32_t *__restrict__ keys, const uint2 *__restric
             }
             double h[3] = {0.0, 0.0, 0.0};
             if (me.x == me.y) {
-                const int p = pt_idx[me.x];
+                const int p = pt_c[me.x];                 // me.x is a camera-major position
                 h[0] = H[3 * (size_t)p]; h[1] = H[3 * (size_t)p + 1]; h[2] = H[3 * (size_t)p + 2];
             }
 #pragma unroll
@@ -1563,7 +1582,7 @@ static size_t ba_layout(BAPlan &pl, unsigned char *base, int nc, int np, int nob
     CARVE(Vinv, double, D * 6 * np);
     CARVE(bp, double, D * 3 * np);
     CARVE(tp, double, D * 3 * np);
-    CARVE(Z, double, D * 18 * nobs);
+    CARVE(Z, double, D * 20 * nobs);     // 160-byte records in camera-major order
     CARVE(Ginv, double, D * 9 * np);       // G [np,6] followed by h = G g_p [np,3]
     pl.pair_keys = nullptr; pl.pair_vals = nullptr; pl.npairs = 0; pl.pair_seg = 0;
     CARVE(U, double, D * (27 * nc + 8));   // [U 21nc | g_c 6nc | cost, ...]: ONE allreduce per linearisation
@@ -1785,8 +1804,11 @@ static int ba_build_pairs(const BAPlan &pl, const int32_t *cam_idx, cudaStream_t
     unsigned long long *v_i = nullptr;
     SFM_CUDA_TRY(cudaMallocAsync(&k_i, sizeof(uint32_t) * npadded, st));
     SFM_CUDA_TRY(cudaMallocAsync(&v_i, sizeof(unsigned long long) * npadded, st));
+    // zpos = inverse of the camera-major permutation, kept in the index's `iota` scratch (the sort is done with it)
+    ba_invert_perm_kernel<<<ceil_div(pl.nobs, 256), 256, 0, st>>>(pl.perm, pl.nobs, pl.iota);
+    SFM_LAUNCH_CHECK();
     ba_pair_interleave_kernel<<<(unsigned)((npadded + 255) / 256), 256, 0, st>>>(
-        k_out, reinterpret_cast<const uint2 *>(v_out), P, seg, npadded, k_i, reinterpret_cast<uint2 *>(v_i));
+        k_out, reinterpret_cast<const uint2 *>(v_out), pl.iota, P, seg, npadded, k_i, reinterpret_cast<uint2 *>(v_i));
     SFM_LAUNCH_CHECK();
     SFM_CUDA_TRY(cudaFreeAsync(k_out, st));
     SFM_CUDA_TRY(cudaFreeAsync(v_out, st));
@@ -2158,7 +2180,13 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
     while (status == -2) {
         // ---- one trial step with damping lambda ----
         mark(0);
-        SFM_CUDA_TRY(cudaMemsetAsync(pl.S, 0, s_bytes, st));
+        // with K11s only the cells of its pattern are ever read (every Schur kernel writes inside the pattern: it was
+        // built from the same pair list); the dense kernel and the dense all-reduce need the whole array
+        if (dag && (!comm || blk_list)) {
+            if ((rc = chol_dag_zero_system(dag, pl.S, pl.ld, st)) != SFM_OK) return rc;
+        } else {
+            SFM_CUDA_TRY(cudaMemsetAsync(pl.S, 0, s_bytes, st));
+        }
         SFM_CUDA_TRY(cudaMemsetAsync(pl.flags + 1, 0, 2 * sizeof(int), st));
         SFM_CUDA_TRY(cudaMemsetAsync(pl.tp, 0, sizeof(double) * 3 * (size_t)np, st));
         if (rank == 0) {      // the camera blocks U + lambda Dc^2, g_c and the padding enter the summed S once
@@ -2175,7 +2203,7 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
             ba_point_prep_kernel<<<ceil_div(np, 256), 256, 0, st>>>(pl.V, pl.gp, pl.Dp, np, lambda, update_D, first_lin,
                                                                    pl.Vinv, pl.bp, pl.gmax, pl.flags + 1, pl.Ginv);
             SFM_LAUNCH_CHECK();
-            ba_schur_z_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(pl.W, nobs, d_pt_idx, pl.Ginv, pl.Z);
+            ba_schur_z_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(pl.W, nobs, d_pt_idx, pl.iota, pl.Ginv, pl.Z);
             SFM_LAUNCH_CHECK();
             static bool sg_attr = false;
             if (!sg_attr) {
@@ -2184,7 +2212,7 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
             }
             const size_t nwarps = pl.npairs / ((size_t)pl.pair_seg * 32);
             ba_schur_gather_kernel<<<(unsigned)(nwarps / (SG_THREADS / 32)), SG_THREADS, SG_SMEM, st>>>(
-                pl.pair_keys, pl.pair_vals, pl.pair_seg, pl.Z, d_pt_idx, pl.Ginv + 6 * (size_t)np, nc, pl.S, pl.ld,
+                pl.pair_keys, pl.pair_vals, pl.pair_seg, pl.Z, pl.pt_c, pl.Ginv + 6 * (size_t)np, nc, pl.S, pl.ld,
                 pl.S + (size_t)pl.npad * pl.ld);
             SFM_LAUNCH_CHECK();
         } else if (!schur_by_rows() && schur_smem_ranges(nc, pl.max_track, rg)) {

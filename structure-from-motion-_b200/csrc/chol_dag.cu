@@ -399,6 +399,8 @@ struct CholDagPlan {
     size_t blob_bytes = 0;
     unsigned epoch = 0;
     int G = 0;
+    uint32_t *d_cells = nullptr;   // (block row << 16 | block col) of every cell of the lower-triangle pattern (in blob)
+    int n_cells = 0;
 };
 
 static int g_dag_grid = 0;
@@ -450,6 +452,11 @@ CholDagPlan *chol_dag_create(const uint8_t *h_pattern, int nb, int order_mode, c
     const size_t o_pvec = take(sizeof(double) * std::max<size_t>((size_t)h.n_part, 1) * CH_NB);
     const char *trace_path = getenv("SFM_CHOL_DAG_TRACE");
     const size_t o_trace = take(trace_path ? sizeof(unsigned long long) * 4 * h.tasks.size() : 0);
+    std::vector<uint32_t> cells;
+    for (int i = 0; i < nb; ++i)
+        for (int j = 0; j <= i; ++j)
+            if (i == j || h_pattern[(size_t)i * nb + j]) cells.push_back(((uint32_t)i << 16) | (uint32_t)j);
+    const size_t o_cells = take(sizeof(uint32_t) * cells.size());
     const size_t o_Lc = take(sizeof(double) * std::max<size_t>(nblk, 1) * DG_BLK);
     p->blob_bytes = off;
     if (cudaMallocAsync(&p->blob, off, st) != cudaSuccess) {
@@ -469,6 +476,7 @@ CholDagPlan *chol_dag_create(const uint8_t *h_pattern, int nb, int order_mode, c
               up(o_bp, h.bwd_ptr.data(), sizeof(int32_t) * h.bwd_ptr.size()) &&
               up(o_bl, h.bwd_list.data(), sizeof(int32_t) * h.bwd_list.size()) &&
               up(o_perm, h.perm.data(), sizeof(int32_t) * nb) &&
+              up(o_cells, cells.data(), sizeof(uint32_t) * cells.size()) &&
               cudaMemsetAsync(base + o_flags, 0, sizeof(unsigned) * (nblk + 2 * nb + 4), st) == cudaSuccess &&
               cudaStreamSynchronize(st) == cudaSuccess;        // the host vectors must outlive the copies
     if (!ok) {
@@ -492,6 +500,8 @@ CholDagPlan *chol_dag_create(const uint8_t *h_pattern, int nb, int order_mode, c
     d.y = reinterpret_cast<double *>(base + o_y);
     d.xe = reinterpret_cast<double *>(base + o_xe);
     d.pvec = reinterpret_cast<double *>(base + o_pvec);
+    p->d_cells = reinterpret_cast<uint32_t *>(base + o_cells);
+    p->n_cells = (int)cells.size();
     d.trace = trace_path ? reinterpret_cast<unsigned long long *>(base + o_trace) : nullptr;
     d.Lc = reinterpret_cast<double *>(base + o_Lc);
     return p;
@@ -517,6 +527,33 @@ int chol_dag_launch(CholDagPlan *p, const double *A, size_t ld, int npad, double
 }
 
 const CholDagHost &chol_dag_host(const CholDagPlan *p) { return p->h; }
+
+// Zero exactly what the factorisation reads: the 48 x 48 cells of the pattern and the right-hand-side row. (A reduced
+// camera system of 1,000 cameras is 295 MB as a dense array and 24 MB in its pattern: the memset of the whole array
+// cost more than the Z pass of the Schur complement.)
+__global__ void __launch_bounds__(256) chol_dag_zero_kernel(double *__restrict__ A, size_t ld, int nb,
+                                                            const uint32_t *__restrict__ cells, int n_cells) {
+    const int b = blockIdx.x;
+    if (b < n_cells) {
+        const uint32_t c = cells[b];
+        double *blk = A + (size_t)(c >> 16) * CH_NB * ld + (size_t)(c & 0xffffu) * CH_NB;
+        for (int e = threadIdx.x; e < DG_BLK / 2; e += 256) {
+            const int r = e / (CH_NB / 2), c2 = e - r * (CH_NB / 2);
+            reinterpret_cast<double2 *>(blk + (size_t)r * ld)[c2] = make_double2(0.0, 0.0);
+        }
+    } else {
+        double *rhs = A + (size_t)nb * CH_NB * ld;
+        for (size_t e = (size_t)(b - n_cells) * 256 + threadIdx.x; e < (size_t)nb * CH_NB; e += (size_t)(gridDim.x - n_cells) * 256)
+            rhs[e] = 0.0;
+    }
+}
+
+int chol_dag_zero_system(CholDagPlan *p, double *A, size_t ld, cudaStream_t st) {
+    if (!p) return SFM_E_INVALID;
+    chol_dag_zero_kernel<<<p->n_cells + 8, 256, 0, st>>>(A, ld, p->h.nb, p->d_cells, p->n_cells);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
 
 // SFM_CHOL_DAG_TRACE=<file>: per-task timestamps of the last launch, written as
 // int64 n_tasks | tasks [n_tasks][12] int32 | trace [n_tasks][4] uint64 (diagnostic, tools/chol_dag_trace.py)
