@@ -180,7 +180,8 @@ typedef struct sfm_ba_options {
     double ftol, xtol, gtol; /* MINPACK / scipy stopping tolerances (reference: scipy default 1e-8) */
     double lambda0;      /* initial damping of (J^T J + lambda D^2); D = Jacobian column norms */
     int32_t reuse_index; /* 1: d_ws still holds the camera-major index of a previous sfm_ba_solve call
-                            on the SAME d_cam_idx / d_pt_idx contents (skips the index build) */
+                            on the SAME d_cam_idx / d_pt_idx contents (skips the index build; d_obs MAY have
+                            changed: the library's camera-major copy of it is refreshed on every call) */
     int32_t reserved;    /* bit 0: record the phase profile of this solve (sfm_ba_last_profile) */
 } sfm_ba_options;
 
@@ -204,6 +205,8 @@ size_t sfm_ba_workspace_bytes(int32_t n_cams, int32_t n_pts, int32_t n_obs);
  * library); the next solve rebuilds what it needs. Returns the number of bytes released through *bytes
  * (may be NULL). */
 int sfm_ba_release_cache(uint64_t *bytes, void *stream);
+/* The same for ONE workspace (call before freeing or re-purposing d_ws; unknown pointers are ignored). */
+int sfm_ba_release_workspace(const void *d_ws, void *stream);
 
 /* Phase profile of the last sfm_ba_solve* call of this process that ran with opts.reserved bit 0 set (CUDA events
  * on the caller's stream; diagnostic, used by bench.py for the multi-GPU time breakdown). HOST out, milliseconds

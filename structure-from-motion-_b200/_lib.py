@@ -70,6 +70,7 @@ SIGNATURES = {
     "sfm_ba_default_options": (None, [c_vp]),
     "sfm_ba_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "sfm_ba_last_profile": (C.c_int, [c_vp]),
+    "sfm_ba_release_workspace": (C.c_int, [c_vp, c_vp]),
     "sfm_ba_release_cache": (C.c_int, [C.c_void_p, C.c_void_p]),
     "sfm_ba_residuals": (C.c_int, [c_f64p, c_f64p, c_f64p, c_i32p, c_i32p, C.c_int32, C.c_int32, C.c_int32,
                                    c_vp, c_f64p, c_f64p, c_vp, C.c_size_t, c_vp]),

@@ -6,7 +6,9 @@ the C ABI (sfm_ba_solve / sfm_ba_residuals). The sparse entry points (`ba_solve_
 reference's dense (n_features x n_images) arrays do not scale."""
 from __future__ import annotations
 
+import collections
 import ctypes as C
+import zlib
 
 import numpy as np
 import torch
@@ -38,9 +40,11 @@ class BAProblem:
         obs = np.ascontiguousarray(obs, np.float64).reshape(-1, 2)
         if not (len(cam_idx) == len(pt_idx) == len(obs)):
             raise ValueError("cam_idx, pt_idx and obs must have one entry per observation")
+        self._order = None
         if len(pt_idx) > 1 and np.any(np.diff(pt_idx) < 0):
             order = np.argsort(pt_idx, kind="stable")       # point-major, original order within a point
             cam_idx, pt_idx, obs = cam_idx[order], pt_idx[order], obs[order]
+            self._order = order
         self.n_cams, self.n_pts, self.n_obs = int(n_cams), int(n_pts), int(len(obs))
         self.K = np.ascontiguousarray(K, np.float64).reshape(3, 3)
         self.d_cam_idx = device.to_device(cam_idx, np.int32)
@@ -52,6 +56,47 @@ class BAProblem:
             raise ValueError("empty bundle adjustment problem")
         self.ws = device.empty((self.ws_bytes,), torch.uint8)
         self._indexed = False          # the workspace holds this problem's camera-major index
+
+    @classmethod
+    def from_device(cls, n_cams, n_pts, d_cam_idx, d_pt_idx, d_obs, K):
+        """The same from device tensors that are already point-sorted (sfm_ba_assemble's output): nothing goes
+        through the host."""
+        self = cls.__new__(cls)
+        self._order = None
+        self.n_cams, self.n_pts, self.n_obs = int(n_cams), int(n_pts), int(d_obs.shape[0])
+        self.K = np.ascontiguousarray(K, np.float64).reshape(3, 3)
+        self.d_cam_idx, self.d_pt_idx, self.d_obs = d_cam_idx.contiguous(), d_pt_idx.contiguous(), d_obs.contiguous()
+        self.ws_bytes = int(_lib.load().sfm_ba_workspace_bytes(self.n_cams, self.n_pts, self.n_obs))
+        if self.ws_bytes == 0:
+            raise ValueError("empty bundle adjustment problem")
+        self.ws = device.empty((self.ws_bytes,), torch.uint8)
+        self._indexed = False
+        return self
+
+    def close(self):
+        """Release what the library caches for this workspace (pair list, K11s plan) -- also run when the object is
+        collected, so a long incremental run does not accumulate the plans of dead problems."""
+        ws, self.ws = getattr(self, "ws", None), None
+        if ws is not None and getattr(self, "_indexed", False):
+            try:
+                _lib.load().sfm_ba_release_workspace(device.ptr(ws), device.stream())
+            except Exception:                       # interpreter shutdown: the process is going away anyway
+                pass
+        self._indexed = False
+
+    def __del__(self):
+        self.close()
+
+    def set_observations(self, obs, K=None):
+        """New measurements for the SAME index structure (cam_idx / pt_idx unchanged): the plan stays valid."""
+        obs = np.ascontiguousarray(obs, np.float64).reshape(-1, 2)
+        if len(obs) != self.n_obs:
+            raise ValueError("set_observations: the number of observations changed")
+        if self._order is not None:
+            obs = obs[self._order]
+        self.d_obs.copy_(torch.from_numpy(obs), non_blocking=True)
+        if K is not None:
+            self.K = np.ascontiguousarray(K, np.float64).reshape(3, 3)
 
     def residuals_device(self, d_cam, d_pts, want_r=True):
         """K8: (d_r [n_obs,2] or None, d_cost [1]) at the given parameters."""
@@ -114,11 +159,45 @@ def release_cache() -> int:
     return int(n.value)
 
 
+# Problems recently solved through the host-array API, keyed by their index structure: everything the library
+# prepares per problem (workspace, camera-major index, K10g pair list, K11s elimination plan) depends only on
+# (cam_idx, pt_idx), so a caller that re-adjusts the same tracks -- every LM restart, every bench step -- pays for it
+# once. Bounded by count and by device bytes; clear_problem_cache() empties it.
+_PROBLEMS: "collections.OrderedDict" = collections.OrderedDict()
+PROBLEM_CACHE_ENTRIES = 4
+PROBLEM_CACHE_BYTES = 8 << 30
+
+
+def clear_problem_cache():
+    while _PROBLEMS:
+        _PROBLEMS.popitem(last=False)[1].close()
+
+
+def _cached_problem(n_cams, n_pts, cam_idx, pt_idx, obs, K):
+    cam_idx = np.ascontiguousarray(cam_idx, np.int32)
+    pt_idx = np.ascontiguousarray(pt_idx, np.int32)
+    key = (int(n_cams), int(n_pts), len(cam_idx), zlib.crc32(cam_idx), zlib.crc32(pt_idx), torch.cuda.current_device())
+    prob = _PROBLEMS.pop(key, None)
+    if prob is not None and not (np.array_equal(prob._key_cam, cam_idx) and np.array_equal(prob._key_pt, pt_idx)):
+        prob.close()                                  # a checksum collision: not the same tracks after all
+        prob = None
+    if prob is None:
+        prob = BAProblem(n_cams, n_pts, cam_idx, pt_idx, obs, K)
+        prob._key_cam, prob._key_pt = cam_idx.copy(), pt_idx.copy()
+    else:
+        prob.set_observations(obs, K)
+    _PROBLEMS[key] = prob
+    while len(_PROBLEMS) > PROBLEM_CACHE_ENTRIES or (len(_PROBLEMS) > 1 and
+                                                      sum(p.ws_bytes for p in _PROBLEMS.values()) > PROBLEM_CACHE_BYTES):
+        _PROBLEMS.popitem(last=False)[1].close()
+    return prob
+
+
 def ba_solve_sparse(cams, pts, cam_idx, pt_idx, obs, K, max_nfev=BA_MAX_NFEV, tol=REF_TOL, verbose=False):
     """Host arrays in/out: cams [Nc,6] = [rotvec, t], pts [Np,3] -> (cams, pts, info)."""
     cams = np.ascontiguousarray(cams, np.float64).reshape(-1, 6)
     pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 3)
-    prob = BAProblem(len(cams), len(pts), cam_idx, pt_idx, obs, K)
+    prob = _cached_problem(len(cams), len(pts), cam_idx, pt_idx, obs, K)
     d_cam, d_pts = device.to_device(cams), device.to_device(pts)
     info = prob.solve_device(d_cam, d_pts, max_nfev, tol, verbose=verbose)
     return d_cam.cpu().numpy(), d_pts.cpu().numpy(), info
@@ -226,30 +305,42 @@ def build_problem_device(all_world_coords, filtered_world_coords, feature_x, fea
 
 def perform_bundle_adjustment(all_world_coords, filtered_world_coords, feature_x, feature_y,
                               filtered_feature_flags, R_set, C_set, K, cam_index, tol=REF_TOL, info=None):
-    """Drop-in for BundleAdjustment.py:113-242 -> (R_set_opt, C_set_opt, all_world_coords_opt)."""
-    prob = build_problem(all_world_coords, filtered_world_coords, feature_x, feature_y,
-                         filtered_feature_flags, R_set, C_set)
-    if prob is None:                                                           # :152-153, :171-172
+    """Drop-in for BundleAdjustment.py:113-242 -> (R_set_opt, C_set_opt, all_world_coords_opt).
+    The observation list of :148-176 is assembled on the device (sfm_ba_assemble): the dense
+    (n_features x n_images) arrays go up once and the point-sorted list never visits the host."""
+    n_cameras = len(R_set)                                                     # :156 (cam_index unused)
+    asm = build_problem_device(all_world_coords, filtered_world_coords, feature_x, feature_y,
+                               filtered_feature_flags, n_cameras) if n_cameras > 0 else None
+    if asm is None:                                                            # :152-153, :171-172
         return R_set, C_set, all_world_coords
-    n_cameras, n_points, n_obs = prob["n_cameras"], prob["n_points"], len(prob["cam_idx"])
+    cams = np.empty((n_cameras, 6))
+    for i in range(n_cameras):                                                 # :183-191, outside the try like the reference
+        R = np.array(R_set[i])
+        cams[i, :3] = Rotation.from_matrix(R).as_rotvec()                      # raises for det <= 0 (scipy), as there
+        cams[i, 3:] = -R @ np.array(C_set[i])
+    n_points, n_obs = asm["n_points"], asm["n_obs"]
     print(f"  Bundle adjustment: {n_cameras} cameras, {n_points} points, {n_obs} observations")
     try:
         m, n = 2 * n_obs, 6 * n_cameras + 3 * n_points
         if m < n:                                                              # scipy's check for 'lm'
             raise ValueError("Method 'lm' doesn't work when the number of residuals is less than the "
                              "number of variables.")
-        cams, pts, res = ba_solve_sparse(prob["cams"], prob["pts"], prob["cam_idx"], prob["pt_idx"],
-                                         prob["obs"], np.array(K, float), BA_MAX_NFEV, tol)
+        prob = BAProblem.from_device(n_cameras, n_points, asm["cam_idx"], asm["pt_idx"], asm["obs"], np.array(K, float))
+        d_cam, d_pts = device.to_device(cams), asm["pts"].contiguous()
+        res = prob.solve_device(d_cam, d_pts, BA_MAX_NFEV, tol)
         if res["status"] < 0:
             raise ValueError("Residuals are not finite in the initial point.")
-        Rm = Rotation.from_rotvec(cams[:, :3]).as_matrix()
+        cams_opt, pts = d_cam.cpu().numpy(), d_pts.cpu().numpy()
+        rows = asm["valid_rows"].cpu().numpy()
+        prob.close()
+        Rm = Rotation.from_rotvec(cams_opt[:, :3]).as_matrix()
         R_set_opt = [Rm[i] for i in range(n_cameras)]                          # :220-228
-        C_set_opt = [-Rm[i].T @ cams[i, 3:] for i in range(n_cameras)]
+        C_set_opt = [-Rm[i].T @ cams_opt[i, 3:] for i in range(n_cameras)]
         all_world_coords_opt = np.array(all_world_coords, copy=True)           # :231-234
-        all_world_coords_opt[prob["valid"]] = pts
+        all_world_coords_opt[rows] = pts
         print(f"  Bundle adjustment completed. Final cost: {res['cost']:.6f}")
         if info is not None:
-            info.update(res, cams=cams, pts=pts)
+            info.update(res, cams=cams_opt, pts=pts)
         return R_set_opt, C_set_opt, all_world_coords_opt
     except _lib.SfmError:
         raise                                  # a broken GPU path must fail loudly, not look like a BA failure

@@ -1859,6 +1859,7 @@ static std::vector<PlanKey> g_plans;
 // unchanged indices (reuse), else on every call.
 static int ba_acquire_index(BAPlan &pl, bool reuse, const void *d_ws, const double2 *obs, const int32_t *d_cam_idx,
                             const int32_t *d_pt_idx, int n_cams, int n_pts, int n_obs, cudaStream_t st) {
+    bool hit = false;
     if (reuse) {
         std::lock_guard<std::mutex> g(g_plan_mu);
         for (const PlanKey &pk : g_plans)
@@ -1867,8 +1868,16 @@ static int ba_acquire_index(BAPlan &pl, bool reuse, const void *d_ws, const doub
                 pl.max_track = pk.max_track;
                 pl.has_dup = pk.has_dup;
                 pl.pair_keys = pk.pair_keys; pl.pair_vals = pk.pair_vals; pl.npairs = pk.npairs; pl.pair_seg = pk.pair_seg;
-                return SFM_OK;
+                hit = true;
+                break;
             }
+    }
+    if (hit) {
+        // the INDEX structure is vouched for, the measurements are not: the camera-major copy of the observations
+        // (what the camera pass K9c reads) is refreshed from the caller's array on every reuse
+        ba_gather_cam_major_kernel<<<ceil_div(n_obs, 256), 256, 0, st>>>(pl.perm, obs, d_pt_idx, n_obs, pl.obs_c, pl.pt_c);
+        SFM_LAUNCH_CHECK();
+        return SFM_OK;
     }
     int rc = ba_build_index(pl, obs, d_cam_idx, d_pt_idx, st);
     if (rc != SFM_OK) return rc;
@@ -1977,6 +1986,24 @@ static int ba_acquire_dag(const BAPlan &pl, const void *d_ws, void *comm, cudaSt
         dag = nullptr;
     }
     *out = dag;
+    return SFM_OK;
+}
+
+// Drops what the library caches for ONE workspace (its index bookkeeping, the K10g pair list, the K11s plan), e.g.
+// when the caller is about to free or reuse that memory. Stream-ordered like sfm_ba_release_cache.
+extern "C" int sfm_ba_release_workspace(const void *d_ws, void *stream) {
+    if (!d_ws) return SFM_E_INVALID;
+    cudaStream_t st = as_stream(stream);
+    std::lock_guard<std::mutex> g(g_plan_mu);
+    for (size_t i = 0; i < g_plans.size(); ++i)
+        if (g_plans[i].ws == d_ws) {
+            PlanKey &q = g_plans[i];
+            if (q.pair_keys) SFM_CUDA_TRY(cudaFreeAsync(q.pair_keys, st));
+            if (q.pair_vals) SFM_CUDA_TRY(cudaFreeAsync(q.pair_vals, st));
+            if (q.dag) chol_dag_destroy(q.dag, st);
+            g_plans.erase(g_plans.begin() + i);
+            break;
+        }
     return SFM_OK;
 }
 

@@ -359,3 +359,38 @@ def test_ba_benchmark_sizes_against_the_sparse_oracle(cuda_device, name):
     assert abs(cost_gpu - ref.cost) / ref.cost < COST_RTOL, (cost_gpu, ref.cost)
     assert abs(_rmse(cost_gpu, nobs) - _rmse(ref.cost, nobs)) < RMSE_ATOL
     assert info["status"] in (1, 2, 3, 4) and cost_gpu <= ref.cost * (1 + COST_RTOL)
+
+
+def test_host_api_reuses_the_plan_of_an_unchanged_index_structure(cuda_device):
+    """ba_solve_sparse caches the problem (workspace, camera-major index, pair list, K11s plan) by the CONTENT of
+    (cam_idx, pt_idx): a second call with the same tracks and new measurements must give exactly what a fresh problem
+    gives, the cache stays bounded, and close() / clear_problem_cache() release the library's side."""
+    from oracle import scenes
+    from sfm_b200 import bundle
+    bundle.clear_problem_cache()
+    sc = scenes.ba_scene(n_cams=12, n_pts=3000, obs_per_pt=6, seed=4)          # > 16384 observations: K10g + K11s plans
+    cams0, pts0 = _x0(sc)
+    a = bundle.ba_solve_sparse(cams0, pts0, sc["cam_idx"], sc["pt_idx"], sc["obs"], sc["K"])
+    assert len(bundle._PROBLEMS) == 1
+    obs2 = sc["obs"] + np.random.default_rng(0).normal(0, 0.3, sc["obs"].shape)
+    b = bundle.ba_solve_sparse(cams0, pts0, sc["cam_idx"].copy(), sc["pt_idx"].copy(), obs2, sc["K"])   # hit
+    assert len(bundle._PROBLEMS) == 1
+    fresh = bundle.BAProblem(12, 3000, sc["cam_idx"], sc["pt_idx"], obs2, sc["K"])
+    from sfm_b200 import device
+    d_c, d_p = device.to_device(cams0), device.to_device(pts0)
+    info = fresh.solve_device(d_c, d_p)
+    assert abs(info["cost"] - b[2]["cost"]) <= 1e-9 * info["cost"] and b[2]["cost"] != a[2]["cost"]
+    assert np.allclose(d_c.cpu().numpy(), b[0], atol=1e-7)
+    fresh.close()
+    # an unsorted caller order is restored on a hit too
+    perm = np.random.default_rng(1).permutation(len(sc["obs"]))
+    c = bundle.ba_solve_sparse(cams0, pts0, sc["cam_idx"][perm], sc["pt_idx"][perm], obs2[perm], sc["K"])
+    c2 = bundle.ba_solve_sparse(cams0, pts0, sc["cam_idx"][perm], sc["pt_idx"][perm], obs2[perm], sc["K"])
+    assert abs(c[2]["cost"] - b[2]["cost"]) <= 1e-9 * b[2]["cost"] and abs(c2[2]["cost"] - c[2]["cost"]) <= 1e-9 * c[2]["cost"]
+    for s in range(6):                                           # different structures: the cache evicts
+        sc_s = scenes.ba_scene(n_cams=5, n_pts=60 + s, obs_per_pt=4, seed=s)
+        cs, ps = _x0(sc_s)
+        bundle.ba_solve_sparse(cs, ps, sc_s["cam_idx"], sc_s["pt_idx"], sc_s["obs"], sc_s["K"])
+    assert len(bundle._PROBLEMS) <= bundle.PROBLEM_CACHE_ENTRIES
+    bundle.clear_problem_cache()
+    assert len(bundle._PROBLEMS) == 0
