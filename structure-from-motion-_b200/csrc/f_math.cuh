@@ -228,6 +228,10 @@ struct FCert {
     float DeT;    // multiplies s = n1 + n2
     float Dn12;   // multiplies |e|
     float C0;     // constant term
+    // certified early reject (no square roots): see f_cert_reject
+    float nDe;    // -(bound on |e_f - e|)
+    float Ea1;    // multiplies min(q1_f, q2_f)
+    float Ea0;    // constant term (+inf: never reject early)
 };
 
 SFM_HD float up_f32(double v) {
@@ -263,7 +267,46 @@ SFM_HD FCert f_cert_setup(const FMat &F, double M1, double M2, double two_thr) {
     c.DeT = ok ? up_f32(DeT) : inf;
     c.Dn12 = up_f32(Dn12);
     c.C0 = up_f32(C0);
+    // ---- early reject. With N_i = n_i + 1e-8 the reference's test (|e|/N1 + |e|/N2)/2 < thr is
+    // |e| (1/N1 + 1/N2) < T, and 1/N1 + 1/N2 > 1/min(N1, N2): a test with |e| >= T min(N1, N2) is an outlier --
+    // no square root needed, compare squares. Bounds, with q_i = n_i^2 exact, Q_i = a_f^2 + b_f^2 of the FP32
+    // intermediates, kap_1 = Sa + Sb >= n_1 (kap_2 likewise), kap = max, and 2 sqrt(x) d <= d (x / kap + kap):
+    //   q_i <= Q_i (1 + 4.01u) + 4.01u kap_i^2 (1 + 4.01u)        (|a_f - a| <= 4.01u Sa, ...)
+    //   Q_i <= q_i,f (1 + 2.1u)                                    (one FMUL + one FFMA rounding)
+    //   min(N1,N2)^2 <= m (1 + eps / kap) + eps kap + eps^2,  m = min(q1, q2)
+    // => min(N)^2 <= A min(q1_f, q2_f) + B,  A = 1 + 7u + eps/kap,  B = 4.02u kap^2 (1 + eps/kap) + eps kap + eps^2,
+    // and |e| >= |e_f| - De. The factor 1.00002 on T^2 covers the FP32 roundings of t, t^2 and of the right-hand
+    // side themselves (< 8u) and the ~1e-12 relative error of the FP64 form the decision is compared with.
+    {
+        const double eps = 1e-8, kap = fmax(fmax(Sa + Sb, Sp + Sq), 1e-300);
+        const double A = 1.0 + 7.0 * u + eps / kap;
+        // + 1e-40: q_i,f may be denormal or flushed (absolute rounding error of a few 2^-149)
+        const double B = 4.02 * u * kap * kap * (1.0 + eps / kap) + eps * kap + eps * eps + 1e-40;
+        const double T2 = T * T * 1.00002;
+        c.nDe = -up_f32(De);
+        c.Ea1 = up_f32(T2 * A);
+        c.Ea0 = (ok && kap < 1e15) ? up_f32(T2 * B) + 1e-36f : inf;
+    }
     return c;
+}
+
+// Certified outlier without square roots: true only if the FP64 decision f_is_inlier is certainly false. e_f and
+// the two squared norms are the FP32 intermediates of f_cert_margin (same operations, same order).
+SFM_HD bool f_cert_reject_from(const FCert &c, float e_abs, float q1, float q2) {
+    const float t = e_abs + c.nDe;
+    const float m = fminf(q1, q2);
+    const float rhs = fmaf(c.Ea1, m, c.Ea0);
+    return t > 0.0f && t * t > rhs;      // strict: an infinite right-hand side (range guard, overflow) never rejects
+}
+
+SFM_HD bool f_cert_reject(const FCert &c, float x1, float y1, float x2, float y2) {
+    float a = fmaf(c.f0, x1, fmaf(c.f1, y1, c.f2));
+    float b = fmaf(c.f3, x1, fmaf(c.f4, y1, c.f5));
+    float cc = fmaf(c.f6, x1, fmaf(c.f7, y1, c.f8));
+    float e = fabsf(fmaf(x2, a, fmaf(y2, b, cc)));
+    float p = fmaf(c.f0, x2, fmaf(c.f3, y2, c.f6));
+    float q = fmaf(c.f1, x2, fmaf(c.f4, y2, c.f7));
+    return f_cert_reject_from(c, e, fmaf(a, a, b * b), fmaf(p, p, q * q));
 }
 
 SFM_HD float sqrt_approx_f32(float s) {

@@ -227,13 +227,14 @@ struct FCert2 {
     u64 f0, f1, f2, f3, f4, f5, f6, f7, f8;
     u64 nT;                     // -2 thr
     u64 DeT, Dn12, C0, U65;     // f_cert_margin's bound constants, 65u
+    u64 nDe, Ea1, Ea0;          // f_cert_reject's constants
 };
 
-template <int PG>  // pairs per uncertainty check
+template <int PG, bool EARLY = true>  // pairs per uncertainty check
 __device__ __forceinline__ void score_pairs(const FCert2 &c, const float4 *__restrict__ rows,
                                             const double *__restrict__ x1x2_rows,
                                             const double *__restrict__ Frow, double two_thr,
-                                            int &cnt) {
+                                            int &cnt, int &vote_fail) {
     unsigned unc = 0;
 #pragma unroll
     for (int k = 0; k < PG; ++k) {
@@ -250,9 +251,24 @@ __device__ __forceinline__ void score_pairs(const FCert2 &c, const float4 *__res
         upk2(q1, q1l, q1h);
         upk2(q2, q2l, q2h);
         upk2(e, el, eh);
+        u64 ea = pk2(fabsf(el), fabsf(eh));
+        if (EARLY) {
+            // certified early reject (f_math.cuh f_cert_reject_from, the same operations on both halves): more than
+            // 95 % of the tests of a RANSAC run are gross outliers, |e| >= T min(N1, N2) by a wide margin; when
+            // every lane of the warp can certify that for both of its tests, the two square roots, the margin and
+            // its error bound are skipped for the pair
+            const u64 t = add2(ea, c.nDe), t2 = mul2(t, t);
+            const u64 rhs = fma2(c.Ea1, pk2(fminf(q1l, q2l), fminf(q1h, q2h)), c.Ea0);
+            float tl, th, t2l, t2h, rl, rh;
+            upk2(t, tl, th);
+            upk2(t2, t2l, t2h);
+            upk2(rhs, rl, rh);
+            const bool rej = tl > 0.0f && th > 0.0f && t2l > rl && t2h > rh;     // strict: see f_cert_reject_from
+            if (__all_sync(0xffffffffu, rej)) continue;
+            ++vote_fail;                       // warp-uniform
+        }
         u64 n1 = pk2(sqrt_approx_f32(q1l), sqrt_approx_f32(q1h));
         u64 n2 = pk2(sqrt_approx_f32(q2l), sqrt_approx_f32(q2h));
-        u64 ea = pk2(fabsf(el), fabsf(eh));
         u64 s = add2(n1, n2);
         u64 lhs = mul2(ea, s);
         u64 d = fma2(mul2(c.nT, n1), n2, lhs);
@@ -294,6 +310,7 @@ __device__ __forceinline__ void score_pairs(const FCert2 &c, const float4 *__res
 // (4.76-5.45 ms at C2; more CTAs per SM spill).
 constexpr int K2P_PAIRS = 2;
 
+template <bool EARLY>
 __global__ void __launch_bounds__(K2_THREADS, 4)
 f_score_packed_kernel(const double *__restrict__ x1x2, int n, const double *__restrict__ Fall, int h,
                       double two_thr, int chunk, int32_t *__restrict__ counts) {
@@ -352,15 +369,17 @@ f_score_packed_kernel(const double *__restrict__ x1x2, int n, const double *__re
         float nT = -c.T, u65 = 3.874301910400391e-6f;
         c2.nT = SFM_DUP(nT); c2.DeT = SFM_DUP(c.DeT); c2.Dn12 = SFM_DUP(c.Dn12);
         c2.C0 = SFM_DUP(c.C0); c2.U65 = SFM_DUP(u65);
+        c2.nDe = SFM_DUP(c.nDe); c2.Ea1 = SFM_DUP(c.Ea1); c2.Ea0 = SFM_DUP(c.Ea0);
 #undef SFM_DUP
     }
     int cnt = 0;
     const double *grow = x1x2 + (size_t)p0 * 4;
     const int npair = np >> 1;
     int j = 0;
+    int unused = 0;
     for (; j + K2P_PAIRS <= npair; j += K2P_PAIRS)
-        score_pairs<K2P_PAIRS>(c2, spair + 2 * j, grow + (size_t)j * 8, Frow, two_thr, cnt);
-    for (; j < npair; ++j) score_pairs<1>(c2, spair + 2 * j, grow + (size_t)j * 8, Frow, two_thr, cnt);
+        score_pairs<K2P_PAIRS, EARLY>(c2, spair + 2 * j, grow + (size_t)j * 8, Frow, two_thr, cnt, unused);
+    for (; j < npair; ++j) score_pairs<1, EARLY>(c2, spair + 2 * j, grow + (size_t)j * 8, Frow, two_thr, cnt, unused);
     if (np & 1) {
         // odd tail of the last chunk: the scalar filter on lane 0 of the last pair
         float4 A = spair[2 * npair], B = spair[2 * npair + 1];
@@ -487,9 +506,21 @@ static int f_score_launch(const double *d_x1x2, int32_t n, const double *d_F, in
         if (scalar32)
             f_score_mixed_kernel<<<grid, K2_THREADS, sizeof(float4) * (size_t)chunk, st>>>(
                 d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);
-        else
-            f_score_packed_kernel<<<grid, K2_THREADS, sizeof(float4) * (size_t)chunk, st>>>(
-                d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);
+        else {
+            // The early reject pays when whole warps certify their pairs as gross outliers: 97 % of the votes at
+            // the reference's 0.06 px (K2 at C2: 4.82 -> 3.97 ms), but a third to a half of them fail at 1.0 px and
+            // then the extra test costs (4.83 -> 5.18 ms; a per-warp adaptive switch lost on both: 4.20 / 5.04).
+            // Thresholds are in pixels in the reference's domain, so the launch picks by threshold. Either kernel
+            // gives the FP64 kernel's counts. SFM_F_SCORE_NO_EARLY / SFM_F_SCORE_EARLY force one of them.
+            static const int forced = getenv("SFM_F_SCORE_NO_EARLY") ? 0 : getenv("SFM_F_SCORE_EARLY") ? 1 : -1;
+            const bool early = forced >= 0 ? forced == 1 : threshold < 0.3;
+            if (!early)
+                f_score_packed_kernel<false><<<grid, K2_THREADS, sizeof(float4) * (size_t)chunk, st>>>(
+                    d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);
+            else
+                f_score_packed_kernel<true><<<grid, K2_THREADS, sizeof(float4) * (size_t)chunk, st>>>(
+                    d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);
+        }
         SFM_LAUNCH_CHECK();
         return SFM_OK;
     }

@@ -231,7 +231,8 @@ def test_certified_fp32_scoring_equals_fp64_kernel(cuda_device):
     xbad = x[:3001].copy()                      # odd count, non-finite coordinates in both pair lanes
     xbad[10, 0] = np.nan; xbad[11, 3] = np.inf; xbad[3000, 1] = np.nan; xbad[2048, 2] = -np.inf
     cases = [(x, 0.06), (x, 1.0), (np.floor(x), 0.06), (x * 1e-3, 1e-4), (x[:1237], 0.5), (x[:9], 0.5),
-             (x[:1025], 0.5), (x[:2050], 0.06), (x[:49999], 0.06), (xbad, 0.5)]
+             (x[:1025], 0.5), (x[:2050], 0.06), (x[:49999], 0.06), (xbad, 0.5), (xbad, 0.06), (x[:1237], 0.29)]
+    # thresholds below 0.3 px run the kernel with the sqrt-free early reject, the others the one without (f_ransac.cu)
     v = C.c_uint64(0)
     for rows, thr in cases:
         m = len(rows)

@@ -145,3 +145,72 @@ def test_certified_fp32_filter_scales_and_degenerate_inputs():
             out = _cert(hs, r, f, thr, chunk)
             assert out[:, 1].sum() == 0, (thr, chunk, out[:, 1])
             assert np.array_equal(out[:, 2], out[:, 3])
+
+
+def _reject(hs, rows, F, thr, chunk=1024):
+    out = np.zeros((len(F), 3), np.int64)
+    hs.hs_f_cert_reject(_p(rows), len(rows), _p(np.ascontiguousarray(F)), len(F), C.c_double(thr), chunk, _p(out))
+    return out
+
+
+def test_early_reject_never_rejects_an_inlier_and_catches_the_gross_outliers():
+    """K2's sqrt-free early reject (f_math.cuh f_cert_reject): |e| >= T min(N1, N2) certifies an outlier. It must
+    never fire on a test the FP64 decision calls an inlier, and it should fire on nearly every gross outlier."""
+    hs = hostsim.load()
+    rng = np.random.default_rng(21)
+    for noise, thr in ((0.3, 0.06), (0.05, 0.06), (0.5, 0.5), (1.0, 3.0)):
+        rows = _two_view(rng, 1500, noise)
+        F = _hypotheses(hs, rows, rng, 200)
+        out = _reject(hs, rows, F, thr)
+        assert out[:, 1].sum() == 0, (noise, thr)
+        assert out[:, 0].sum() > 0.9 * out[:, 2].sum(), (noise, thr, out[:, 0].sum(), out[:, 2].sum())
+
+
+def test_early_reject_on_tests_swept_across_its_boundary():
+    """Correspondences moved off the epipolar line by thr x 2^[-1, 3]: the sweep crosses both the inlier threshold
+    and the reject boundary (about twice the threshold when the two line norms are alike)."""
+    hs = hostsim.load()
+    rng = np.random.default_rng(22)
+    base = _two_view(rng, 600, 0.0, outliers=0.0)
+    F = _hypotheses(hs, base, rng, 40)
+    thr = 0.06
+    rejected = kept_outliers = 0
+    for Fk in F:
+        Fm = Fk.reshape(3, 3)
+        rows = base.copy()
+        x1h = np.column_stack([rows[:, :2], np.ones(len(rows))])
+        l2 = x1h @ Fm.T
+        nrm = np.linalg.norm(l2[:, :2], axis=1)
+        d = (np.sum(l2[:, :2] * rows[:, 2:], axis=1) + l2[:, 2]) / nrm
+        rows[:, 2:] -= (d / nrm)[:, None] * l2[:, :2]
+        target = thr * 2.0 ** rng.uniform(-1.0, 3.0, len(rows)) * rng.choice([-1.0, 1.0], len(rows))
+        rows[:, 2:] += (target / nrm)[:, None] * l2[:, :2]
+        out = _reject(hs, np.ascontiguousarray(rows), Fk[None], thr)
+        assert out[0, 1] == 0
+        rejected += out[0, 0]
+        kept_outliers += out[0, 2] - out[0, 0]
+    assert rejected > 0 and kept_outliers > 0          # the sweep really straddles the boundary
+
+
+def test_early_reject_scales_and_degenerate_inputs():
+    hs = hostsim.load()
+    rng = np.random.default_rng(23)
+    rows = _two_view(rng, 800, 0.2)
+    F = _hypotheses(hs, rows, rng, 30)
+    cases = []
+    for fs in (1e-25, 1e-8, 1.0, 1e8, 1e25):
+        cases.append((rows, F * fs, 0.06))
+    for cs in (1e-3, 1e3, 1e7):
+        r2 = np.ascontiguousarray(rows * cs)
+        cases.append((r2, _hypotheses(hs, r2, rng, 30), 0.06 * cs))
+    Fbad = F.copy()
+    Fbad[0, 3] = np.nan
+    Fbad[1, 8] = np.inf
+    Fbad[2] = 0.0
+    cases.append((rows, Fbad, 0.06))
+    cases.append((rows, F, 0.0))                        # threshold 0: nothing is an inlier
+    cases.append((rows, F, 1e6))                        # everything is
+    for r, f, thr in cases:
+        with np.errstate(all="ignore"):
+            out = _reject(hs, r, f, thr)
+        assert out[:, 1].sum() == 0
