@@ -163,7 +163,7 @@ def run_single_gpu(args, peaks, peak_src, flush):
     sc5, cams5, pts5 = _scene(C5)
     prob5 = bundle.BAProblem(C5["n_cams"], C5["n_pts"], sc5["cam_idx"], sc5["pt_idx"], sc5["obs"], sc5["K"])
     n5, p5 = len(sc5["obs"]), C5["n_pts"]
-    ms5, infos5 = time_solves(prob5, cams5, pts5, 3, 1, flush)
+    ms5, infos5 = time_solves(prob5, cams5, pts5, 3, 2, flush)
     its5 = sum(i["n_linearisations"] for i in infos5)
     passes = {}
     for name, which, nbytes in (("K9p ba_point_pass_kernel", 1, k9p_bytes(n5, p5)),

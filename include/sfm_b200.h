@@ -196,6 +196,9 @@ typedef struct sfm_ba_result {
     int32_t n_chol_fail; /* trial steps rejected because S was not numerically positive definite */
 } sfm_ba_result;
 
+/* One process per GPU: the BA entry points bind their per-device state (kernel attributes, side stream, plan
+ * cache) to the device that is current at the FIRST call; calls made with another device current return
+ * SFM_E_INVALID (message in sfm_last_cuda_error()). */
 void sfm_ba_default_options(sfm_ba_options *opts);
 size_t sfm_ba_workspace_bytes(int32_t n_cams, int32_t n_pts, int32_t n_obs);
 /* Everything sfm_ba_solve* needs lives in the caller's workspace except the plan-time pair list of the

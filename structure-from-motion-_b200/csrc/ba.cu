@@ -1858,7 +1858,8 @@ static std::vector<PlanKey> g_plans;
 // Index structures: built once per (workspace, problem shape) when the caller vouches for
 // unchanged indices (reuse), else on every call.
 static int ba_acquire_index(BAPlan &pl, bool reuse, const void *d_ws, const double2 *obs, const int32_t *d_cam_idx,
-                            const int32_t *d_pt_idx, int n_cams, int n_pts, int n_obs, cudaStream_t st) {
+                            const int32_t *d_pt_idx, int n_cams, int n_pts, int n_obs, cudaStream_t st,
+                            bool refresh_obs = true) {
     bool hit = false;
     if (reuse) {
         std::lock_guard<std::mutex> g(g_plan_mu);
@@ -1872,6 +1873,7 @@ static int ba_acquire_index(BAPlan &pl, bool reuse, const void *d_ws, const doub
                 break;
             }
     }
+    if (hit && !refresh_obs) return SFM_OK;
     if (hit) {
         // the INDEX structure is vouched for, the measurements are not: the camera-major copy of the observations
         // (what the camera pass K9c reads) is refreshed from the caller's array on every reuse
@@ -2007,8 +2009,29 @@ extern "C" int sfm_ba_release_workspace(const void *d_ws, void *stream) {
     return SFM_OK;
 }
 
+namespace sfm { void record_error_text(const char *msg); }
+
 static int ba_prepare(BAPlan &pl, void *d_ws, size_t ws_bytes, int32_t n_cams, int32_t n_pts, int32_t n_obs) {
     if (n_cams < 1 || n_pts < 1 || n_obs < 1 || !d_ws) return SFM_E_INVALID;
+    {
+        // One process per GPU (the deployment model: torch.distributed, one rank per device). The kernel attributes,
+        // cooperative grid sizes, the side stream / events and the plan cache are set up once, on the device of the
+        // first call; a call on another device would launch kernels without their shared-memory opt-in on a stream
+        // of the wrong device, so it is refused instead.
+        static std::mutex dev_mu;
+        static int bound_dev = -1;
+        int dev = -1;
+        SFM_CUDA_TRY(cudaGetDevice(&dev));
+        std::lock_guard<std::mutex> g(dev_mu);
+        if (bound_dev < 0) bound_dev = dev;
+        else if (dev != bound_dev) {
+            char msg[160];
+            snprintf(msg, sizeof(msg), "sfm_ba_*: this process bound the BA path to device %d on its first call; "
+                     "current device is %d (one process per GPU)", bound_dev, dev);
+            record_error_text(msg);
+            return SFM_E_INVALID;
+        }
+    }
     unsigned char *base = reinterpret_cast<unsigned char *>(align_up((size_t)d_ws, 256));
     size_t need = ba_layout(pl, base, n_cams, n_pts, n_obs);
     if ((size_t)(base - (unsigned char *)d_ws) + need > ws_bytes) return SFM_E_WORKSPACE;
@@ -2142,7 +2165,8 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
         SFM_CUDA_TRY(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
         SFM_CUDA_TRY(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
     }
-    auto linearise = [&](int first) -> int {
+    // the work of one linearisation; `forked` tells the caller whether the side stream is running and unjoined
+    auto linearise_body = [&](int first, bool &forked) -> int {
         int r;
         SFM_CUDA_TRY(cudaMemsetAsync(pl.gmax, 0, 8, st));
         cudaStream_t cs = st;                                  // stream of the camera pass
@@ -2150,6 +2174,7 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
             SFM_CUDA_TRY(cudaEventRecord(ev_fork, st));
             SFM_CUDA_TRY(cudaStreamWaitEvent(side, ev_fork, 0));
             cs = side;
+            forked = true;
         }
         if (pl.nchunks) {
             ba_camera_pass_kernel<<<pl.nchunks, K9C_THREADS, 0, cs>>>(K, pl.camlin[cur], pl.pts[cur], pl.obs_c, pl.pt_c,
@@ -2160,7 +2185,6 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
         ba_cam_finalize_kernel<<<ceil_div(nc, 8), 256, 0, cs>>>(pl.Upart, pl.chunk_ptr, nc, pl.U, pl.gc, first,
                                                                comm ? nullptr : pl.Dc, pl.gmax);
         SFM_LAUNCH_CHECK();
-        if (!comm) SFM_CUDA_TRY(cudaEventRecord(ev_join, side));
         if ((r = launch_point_pass(pl, K, pl.camlin[cur], pl.pts[cur], obs, d_cam_idx, d_pt_idx, st)) != SFM_OK) return r;
         ba_reduce_scalars_kernel<<<1, 256, 0, st>>>(pl.costpart, pl.grid_obs, nullptr, 0, nullptr, nullptr, nullptr, pl.red1);
         SFM_LAUNCH_CHECK();
@@ -2168,10 +2192,22 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
             if ((r = comm_allreduce_sum_f64(comm, pl.U, 27 * (size_t)nc + 1, st)) != SFM_OK) return r;
             ba_cam_scale_kernel<<<ceil_div(nc, 128), 128, 0, st>>>(pl.U, pl.gc, nc, first, pl.Dc, pl.gmax);
             SFM_LAUNCH_CHECK();
-        } else {
-            SFM_CUDA_TRY(cudaStreamWaitEvent(st, ev_join, 0));
         }
         return SFM_OK;
+    };
+    auto linearise = [&](int first) -> int {
+        bool forked = false;
+        const int r = linearise_body(first, forked);
+        if (forked) {
+            // join on EVERY path: an error return must not leave the caller's stream ahead of the side stream
+            // (the next call would fork from a stream the side stream is not ordered against)
+            cudaError_t e1 = cudaEventRecord(ev_join, side), e2 = cudaStreamWaitEvent(st, ev_join, 0);
+            if (r == SFM_OK && (e1 != cudaSuccess || e2 != cudaSuccess)) {
+                record_cuda_error(e1 != cudaSuccess ? e1 : e2, "join of the camera-pass stream");
+                return SFM_E_CUDA;
+            }
+        }
+        return r;
     };
 
     static thread_local cudaEvent_t pe_lin0[2] = {};
@@ -2462,7 +2498,10 @@ extern "C" int sfm_ba_linearise(const double *d_cam, const double *d_pts, const 
     KParam K;
     for (int i = 0; i < 9; ++i) K.k[i] = h_K[i];
     const double2 *obs = reinterpret_cast<const double2 *>(d_obs);
-    if ((rc = ba_acquire_index(pl, reuse_index != 0, d_ws, obs, d_cam_idx, d_pt_idx, n_cams, n_pts, n_obs, st)) != SFM_OK)
+    // bit 3 (same state as the previous call, for timing one pass alone) also skips the refresh of the camera-major
+    // observation copy
+    if ((rc = ba_acquire_index(pl, reuse_index != 0, d_ws, obs, d_cam_idx, d_pt_idx, n_cams, n_pts, n_obs, st,
+                               !(which & 8))) != SFM_OK)
         return rc;
     if (!(which & 8) && (rc = launch_cam_linearise(pl, K, d_cam, pl.camlin[0], st)) != SFM_OK) return rc;
     if (which & 1) {
