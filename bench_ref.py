@@ -136,10 +136,11 @@ def ba_leg(pool):
                     "measured_lm_iterations_s": [1.0 / r["s_per_lm_iteration"] for r in rs],
                     "extrapolated_lm_iterations_s": {"C3": ext(cfg.C3), "C5": ext(cfg.C5)},
                     "note": "extrapolation by t_iter = c * Nobs * (6 Nc + 3 Np); NOT a measurement"}
-    best = out.get("reference") or out["port"]
-    out["value"] = best["measured_lm_iterations_s"][-1]
-    out["config"] = {"workload": "synthetic BA at the largest size the host finishes: "
-                                 f"{runs[len(runs) // 2 if kind() == 'reference' else -1]['cameras']} cameras"}
+    tag = "reference" if "reference" in out else "port"
+    last = [r for r in runs if r["kind"] == tag][-1]
+    out["value"] = 1.0 / last["s_per_lm_iteration"]
+    out["config"] = {"workload": f"synthetic BA at the largest size timed on the host ({tag}): {last['cameras']} cameras, "
+                                 f"{last['points']} points, {last['observations']} observations"}
     return out
 
 
