@@ -94,7 +94,12 @@ class BAProblem:
             raise ValueError("set_observations: the number of observations changed")
         if self._order is not None:
             obs = obs[self._order]
-        self.d_obs.copy_(torch.from_numpy(obs), non_blocking=True)
+        # through a pinned staging buffer owned by the problem: a pageable source makes the copy synchronous and
+        # half as fast (3.2 MB at C3)
+        if getattr(self, "_pin_obs", None) is None:
+            self._pin_obs = torch.empty((self.n_obs, 2), dtype=torch.float64, pin_memory=True)
+        self._pin_obs.numpy()[...] = obs
+        self.d_obs.copy_(self._pin_obs, non_blocking=True)
         if K is not None:
             self.K = np.ascontiguousarray(K, np.float64).reshape(3, 3)
 
@@ -174,18 +179,31 @@ def clear_problem_cache():
 
 
 def _cached_problem(n_cams, n_pts, cam_idx, pt_idx, obs, K):
+    cam_in, pt_in = cam_idx, pt_idx
     cam_idx = np.ascontiguousarray(cam_idx, np.int32)
     pt_idx = np.ascontiguousarray(pt_idx, np.int32)
-    key = (int(n_cams), int(n_pts), len(cam_idx), zlib.crc32(cam_idx), zlib.crc32(pt_idx), torch.cuda.current_device())
+    dev = torch.cuda.current_device()
+    # fast path: the very array objects of the most recent call (an LM restart, a bench step) -- found by identity,
+    # still verified by content (the caller may have written into them), without the two checksum passes
+    key = None
+    if _PROBLEMS:
+        k_last, p_last = next(reversed(_PROBLEMS.items()))
+        if p_last._key_ids == (id(cam_in), id(pt_in)) and k_last[:3] == (int(n_cams), int(n_pts), len(cam_idx)) and \
+                k_last[-1] == dev:
+            key = k_last
+    if key is None:
+        key = (int(n_cams), int(n_pts), len(cam_idx), zlib.crc32(cam_idx), zlib.crc32(pt_idx), dev)
     prob = _PROBLEMS.pop(key, None)
     if prob is not None and not (np.array_equal(prob._key_cam, cam_idx) and np.array_equal(prob._key_pt, pt_idx)):
-        prob.close()                                  # a checksum collision: not the same tracks after all
+        prob.close()                                  # changed in place, or a checksum collision: not the same tracks
         prob = None
+        key = (int(n_cams), int(n_pts), len(cam_idx), zlib.crc32(cam_idx), zlib.crc32(pt_idx), dev)
     if prob is None:
         prob = BAProblem(n_cams, n_pts, cam_idx, pt_idx, obs, K)
         prob._key_cam, prob._key_pt = cam_idx.copy(), pt_idx.copy()
     else:
         prob.set_observations(obs, K)
+    prob._key_ids = (id(cam_in), id(pt_in))
     _PROBLEMS[key] = prob
     while len(_PROBLEMS) > PROBLEM_CACHE_ENTRIES or (len(_PROBLEMS) > 1 and
                                                       sum(p.ws_bytes for p in _PROBLEMS.values()) > PROBLEM_CACHE_BYTES):

@@ -387,6 +387,20 @@ def test_host_api_reuses_the_plan_of_an_unchanged_index_structure(cuda_device):
     c = bundle.ba_solve_sparse(cams0, pts0, sc["cam_idx"][perm], sc["pt_idx"][perm], obs2[perm], sc["K"])
     c2 = bundle.ba_solve_sparse(cams0, pts0, sc["cam_idx"][perm], sc["pt_idx"][perm], obs2[perm], sc["K"])
     assert abs(c[2]["cost"] - b[2]["cost"]) <= 1e-9 * b[2]["cost"] and abs(c2[2]["cost"] - c[2]["cost"]) <= 1e-9 * c[2]["cost"]
+    # the identity fast path must not trust objects whose CONTENT changed in place
+    ci, pi = sc["cam_idx"].copy(), sc["pt_idx"].copy()
+    d1 = bundle.ba_solve_sparse(cams0, pts0, ci, pi, obs2, sc["K"])
+    d2 = bundle.ba_solve_sparse(cams0, pts0, ci, pi, obs2, sc["K"])             # identity hit
+    assert abs(d2[2]["cost"] - d1[2]["cost"]) <= 1e-9 * d1[2]["cost"]
+    keep = pi < 2999                                             # drop the last point's observations, same objects reused
+    ci2, pi2, ob2 = ci[keep], pi[keep], obs2[keep]
+    ci[:len(ci2)] = ci2                                          # (write into the old objects too: must be noticed)
+    d3 = bundle.ba_solve_sparse(cams0, pts0[:2999], ci2, pi2, ob2, sc["K"])
+    f3 = bundle.BAProblem(12, 2999, ci2, pi2, ob2, sc["K"])
+    d_c3, d_p3 = device.to_device(cams0), device.to_device(pts0[:2999])
+    i3 = f3.solve_device(d_c3, d_p3)
+    assert abs(i3["cost"] - d3[2]["cost"]) <= 1e-9 * i3["cost"]
+    f3.close()
     for s in range(6):                                           # different structures: the cache evicts
         sc_s = scenes.ba_scene(n_cams=5, n_pts=60 + s, obs_per_pt=4, seed=s)
         cs, ps = _x0(sc_s)
