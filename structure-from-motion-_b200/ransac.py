@@ -115,8 +115,8 @@ def f_ransac_host(points1, points2, samples, threshold, want_err=False, want_all
 _PINNED: dict = {}
 STREAM_MIN_HYPOTHESES = 16384      # below this one sfm_f_ransac call is cheaper than chunking
 STREAM_CHUNKS = 2
-STREAM_FIRST_CHUNK = 3072
-STREAM_GROWTH = 2.5
+STREAM_FIRST_CHUNK = 4096
+STREAM_GROWTH = 2.0
 
 
 def _side_stream() -> torch.cuda.Stream:
@@ -137,6 +137,17 @@ def _pinned_i32(rows: int, cols: int) -> torch.Tensor:
     return buf[:need].view(rows, cols)
 
 
+def _pinned_f64(rows: int, cols: int) -> torch.Tensor:
+    """Grow-only pinned staging buffer for the correspondences (a call ends with a synchronising read, so the
+    buffer is free again when the next call fills it)."""
+    need = rows * cols
+    buf = _PINNED.get("points")
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.float64, pin_memory=True)
+        _PINNED["points"] = buf
+    return buf[:need].view(rows, cols)
+
+
 def f_ransac_stream(points1, points2, threshold, n_max, chunks=STREAM_CHUNKS):
     """GetInliersRANSAC's hot loop with the host work overlapped: the reference's RNG stream is
     replayed chunk by chunk into pinned memory while the GPU generates and scores the previous
@@ -146,7 +157,16 @@ def f_ransac_stream(points1, points2, threshold, n_max, chunks=STREAM_CHUNKS):
     p1 = np.ascontiguousarray(points1, np.float64)
     p2 = np.ascontiguousarray(points2, np.float64)
     n, h = len(p1), int(n_max)
-    d_x = torch.cat([device.to_device(p1), device.to_device(p2)], dim=1)     # [n,4] rows (x1,y1,x2,y2), built on device
+    # [n,4] rows (x1,y1,x2,y2). Both point sets go through ONE pinned buffer (two contiguous host copies, one
+    # asynchronous upload that overlaps the replay of the first chunk; a pageable source blocks the host for
+    # ~0.7 ms at 50k correspondences) and are interleaved on the device
+    pin_x = _pinned_f64(2 * n, 2)
+    hx = pin_x.numpy()
+    np.copyto(hx[:n], p1)
+    np.copyto(hx[n:], p2)
+    d_pp = device.empty((2 * n, 2), torch.float64)
+    d_pp.copy_(pin_x, non_blocking=True)
+    d_x = torch.cat([d_pp[:n], d_pp[n:]], dim=1)
     st = device.stream()
     r = _alloc_result(n, h, False)
     key = device.empty((1,), torch.int64)
@@ -154,8 +174,8 @@ def f_ransac_stream(points1, points2, threshold, n_max, chunks=STREAM_CHUNKS):
     pinned = _pinned_i32(h, 8)
     host = pinned.numpy()
     # chunk schedule: a small first chunk (the only one the GPU waits for), then growing by STREAM_GROWTH per
-    # chunk -- the replay runs ~2.9x faster than K2 scores (17 vs 49 ns per hypothesis on the B200 box), so the
-    # CPU stays ahead -- up to h / chunks
+    # chunk -- the replay runs ~2.2x faster than K2 scores (18 vs 40 ns per hypothesis on the B200 box), so the
+    # CPU stays ahead at a growth of 2 -- up to h / chunks (tools/fransac_e2e_trace.py prints the timeline)
     big = max(1, -(-h // max(1, int(chunks))))
     sizes, c = [], min(big, STREAM_FIRST_CHUNK)
     while sum(sizes) < h:
