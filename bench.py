@@ -277,19 +277,24 @@ def run_ours(args, rank, world):
     achieved = alg_bytes / (k2_ms * 1e-3) / 1e9
     tests = float(N_PTS) * N_HYP
     fma_peak = 148 * 128 * 1.965e9          # FP32 FMA lanes x clock: 119-125 of 128 per clock and SM measured
-    ops_per_test = 19.2                      # 19 on the early-reject path + 7 more for the ~3 % of pairs whose vote fails
+    # executed packed-FP32 lane operations per test, counted by ncu (profiles/r02_k2_two_stage_ncu_full.txt): 13 when
+    # the group's first-stage vote passes (86 % of the groups at C2), the repeated stage, F^T x2 and the second norm
+    # (+20) for the groups that fail it, the square-root path for the ~6 % of pairs that fail the second stage
+    ops_per_test = 14.16
     lane_ops = ops_per_test * tests / (k2_ms * 1e-3)
     roofline = {"bound": "fp32_pipe", "kernel": "f_score_packed_kernel (K2)", "achieved": lane_ops / 1e12,
                 "peak": fma_peak / 1e12, "unit": "T FMA-lane-op/s", "frac": lane_ops / fma_peak,
                 "traffic": _ncu_traffic("f_score_packed_kernel"), "kernel_ms": k2_ms,
                 "peak_source": "148 SMs x 128 FP32 lanes x 1.965 GHz (max SM clock); profiles/r01_ubench_fp32_b200.txt "
                                "measures 119 (FFMA) and 125 (FFMA2, broadcast operands) of 128 lanes per clock and SM",
-                "what": "certified FP32 filter on packed FFMA2/FMUL2/FADD2 with a certified sqrt-free early reject "
-                        "(round 2): 19 FMA-lane operations per (hypothesis, correspondence) test when the warp certifies "
-                        "its pairs as gross outliers (97 % of the votes at 0.06 px), 26 + 2 MUFU.SQRT otherwise (round 1: "
-                        "23 + 2 MUFU for every test); 2e-4 of the tests are redone in FP64; tests per launch = N x H. "
-                        "frac counts the operations EXECUTED, so a kernel that does less work per test shows a "
-                        "similar fraction at a higher hypotheses/s",
+                "what": "certified FP32 filter on packed FFMA2/FMUL2/FADD2 with a certified, sqrt-free, TWO-STAGE early "
+                        "reject (round 2): 13 FMA-lane operations per (hypothesis, correspondence) test when the warp "
+                        "certifies a group of 4 correspondences as gross outliers from F x1 and one line norm alone (86 % "
+                        "of the groups at 0.06 px), +6 for F^T x2 and the second norm when that vote fails, 26 + 2 "
+                        "MUFU.SQRT on the full path (round 1: 23 + 2 MUFU for every test); 14.16 executed on average "
+                        "(ncu); 2e-4 of the tests are redone in FP64; tests per launch = N x H. frac counts the "
+                        "operations EXECUTED, so a kernel that does less work per test shows a similar fraction at a "
+                        "higher hypotheses/s",
                 "fma_lane_ops_per_test": ops_per_test,
                 "tests_per_launch": tests,
                 "why_not_hbm": "the 1.6 MB correspondence set is staged in shared memory and re-read by every "

@@ -299,6 +299,24 @@ SFM_HD bool f_cert_reject_from(const FCert &c, float e_abs, float q1, float q2) 
     return t > 0.0f && t * t > rhs;      // strict: an infinite right-hand side (range guard, overflow) never rejects
 }
 
+// First stage of the same certificate, from ONE of the two squared norms: fmaf is monotone in its operands and
+// Ea1 > 0, so the right-hand side built from q1 is never below the one built from min(q1, q2) -- whatever this
+// rejects, f_cert_reject_from rejects (tests/test_hostsim_f.py checks the implication). It needs neither F^T x2
+// nor the second norm, which is what K2 saves on the ~93 % of its votes that pass here.
+SFM_HD bool f_cert_reject_stage1_from(const FCert &c, float e_abs, float q1) {
+    const float t = e_abs + c.nDe;
+    const float rhs = fmaf(c.Ea1, q1, c.Ea0);
+    return t > 0.0f && t * t > rhs;
+}
+
+SFM_HD bool f_cert_reject_stage1(const FCert &c, float x1, float y1, float x2, float y2) {
+    float a = fmaf(c.f0, x1, fmaf(c.f1, y1, c.f2));
+    float b = fmaf(c.f3, x1, fmaf(c.f4, y1, c.f5));
+    float cc = fmaf(c.f6, x1, fmaf(c.f7, y1, c.f8));
+    float e = fabsf(fmaf(x2, a, fmaf(y2, b, cc)));
+    return f_cert_reject_stage1_from(c, e, fmaf(a, a, b * b));
+}
+
 SFM_HD bool f_cert_reject(const FCert &c, float x1, float y1, float x2, float y2) {
     float a = fmaf(c.f0, x1, fmaf(c.f1, y1, c.f2));
     float b = fmaf(c.f3, x1, fmaf(c.f4, y1, c.f5));

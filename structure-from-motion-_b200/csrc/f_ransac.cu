@@ -236,6 +236,36 @@ __device__ __forceinline__ void score_pairs(const FCert2 &c, const float4 *__res
                                             const double *__restrict__ Frow, double two_thr,
                                             int &cnt, int &vote_fail) {
     unsigned unc = 0;
+    if (EARLY && PG > 1) {
+        // the first-stage certificate (f_cert_reject_stage1_from) for ALL pairs of the group with one vote: the
+        // pairs' chains interleave, and the common case (every test of the group a gross outlier: 86 % of the
+        // groups at C2) costs 13 packed operations per pair, 4 compares and one vote -- no F^T x2, no second norm,
+        // no square root. A failed vote falls through to the per-pair path below, which repeats the stage for
+        // its pair (cheaper than keeping the intermediates alive: 64 registers at 4 CTAs per SM is the measured
+        // optimum; 3 CTAs 2.96 ms, 5 CTAs 3.26 ms, 4 pairs per vote 3.08 ms, 2 pairs 2.82 ms)
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < PG; ++k) {
+            float4 A = rows[2 * k], B = rows[2 * k + 1];
+            u64 x1 = pk2(A.x, A.y), y1 = pk2(A.z, A.w), x2 = pk2(B.x, B.y), y2 = pk2(B.z, B.w);
+            u64 a = fma2(c.f0, x1, fma2(c.f1, y1, c.f2));
+            u64 b = fma2(c.f3, x1, fma2(c.f4, y1, c.f5));
+            u64 cc = fma2(c.f6, x1, fma2(c.f7, y1, c.f8));
+            u64 e = fma2(x2, a, fma2(y2, b, cc));
+            u64 q1 = fma2(a, a, mul2(b, b));
+            float el, eh, tl, th, t2l, t2h, rl, rh;
+            upk2(e, el, eh);
+            const u64 t = add2(pk2(fabsf(el), fabsf(eh)), c.nDe), rhs1 = fma2(c.Ea1, q1, c.Ea0);
+            upk2(t, tl, th);
+            // t |t| instead of (t > 0 && t t > rhs): the right-hand side is positive (Ea0 >= 1e-36) or +inf, so a
+            // non-positive t fails the comparison by itself, and for t > 0 the product is the same t t
+            const u64 t2 = mul2(t, pk2(fabsf(tl), fabsf(th)));
+            upk2(t2, t2l, t2h);
+            upk2(rhs1, rl, rh);
+            ok = ok && t2l > rl && t2h > rh;
+        }
+        if (__all_sync(0xffffffffu, ok)) return;
+    }
 #pragma unroll
     for (int k = 0; k < PG; ++k) {
         float4 A = rows[2 * k], B = rows[2 * k + 1];
@@ -244,28 +274,42 @@ __device__ __forceinline__ void score_pairs(const FCert2 &c, const float4 *__res
         u64 b = fma2(c.f3, x1, fma2(c.f4, y1, c.f5));
         u64 cc = fma2(c.f6, x1, fma2(c.f7, y1, c.f8));
         u64 e = fma2(x2, a, fma2(y2, b, cc));
-        u64 p = fma2(c.f0, x2, fma2(c.f3, y2, c.f6));
-        u64 q = fma2(c.f1, x2, fma2(c.f4, y2, c.f7));
-        u64 q1 = fma2(a, a, mul2(b, b)), q2 = fma2(p, p, mul2(q, q));
+        u64 q1 = fma2(a, a, mul2(b, b));
         float q1l, q1h, q2l, q2h, el, eh;
         upk2(q1, q1l, q1h);
-        upk2(q2, q2l, q2h);
         upk2(e, el, eh);
         u64 ea = pk2(fabsf(el), fabsf(eh));
+        u64 p, q, q2;
         if (EARLY) {
             // certified early reject (f_math.cuh f_cert_reject_from, the same operations on both halves): more than
             // 95 % of the tests of a RANSAC run are gross outliers, |e| >= T min(N1, N2) by a wide margin; when
             // every lane of the warp can certify that for both of its tests, the two square roots, the margin and
-            // its error bound are skipped for the pair
+            // its error bound are skipped for the pair. Two stages: first against the norm already at hand
+            // (f_cert_reject_stage1_from: implies the full certificate, passes ~93 % of the votes at C2, and spares
+            // F^T x2 and the second norm), then against min(q1, q2).
             const u64 t = add2(ea, c.nDe), t2 = mul2(t, t);
-            const u64 rhs = fma2(c.Ea1, pk2(fminf(q1l, q2l), fminf(q1h, q2h)), c.Ea0);
             float tl, th, t2l, t2h, rl, rh;
             upk2(t, tl, th);
             upk2(t2, t2l, t2h);
+            const bool pos = tl > 0.0f && th > 0.0f;
+            {
+                const u64 rhs1 = fma2(c.Ea1, q1, c.Ea0);
+                upk2(rhs1, rl, rh);
+                if (__all_sync(0xffffffffu, pos && t2l > rl && t2h > rh)) continue;     // strict: see f_cert_reject_from
+            }
+            p = fma2(c.f0, x2, fma2(c.f3, y2, c.f6));
+            q = fma2(c.f1, x2, fma2(c.f4, y2, c.f7));
+            q2 = fma2(p, p, mul2(q, q));
+            upk2(q2, q2l, q2h);
+            const u64 rhs = fma2(c.Ea1, pk2(fminf(q1l, q2l), fminf(q1h, q2h)), c.Ea0);
             upk2(rhs, rl, rh);
-            const bool rej = tl > 0.0f && th > 0.0f && t2l > rl && t2h > rh;     // strict: see f_cert_reject_from
-            if (__all_sync(0xffffffffu, rej)) continue;
+            if (__all_sync(0xffffffffu, pos && t2l > rl && t2h > rh)) continue;
             ++vote_fail;                       // warp-uniform
+        } else {
+            p = fma2(c.f0, x2, fma2(c.f3, y2, c.f6));
+            q = fma2(c.f1, x2, fma2(c.f4, y2, c.f7));
+            q2 = fma2(p, p, mul2(q, q));
+            upk2(q2, q2l, q2h);
         }
         u64 n1 = pk2(sqrt_approx_f32(q1l), sqrt_approx_f32(q1h));
         u64 n2 = pk2(sqrt_approx_f32(q2l), sqrt_approx_f32(q2h));
@@ -306,12 +350,13 @@ __device__ __forceinline__ void score_pairs(const FCert2 &c, const float4 *__res
     }
 }
 
-// Two pairs per uncertainty vote and 4 CTAs per SM: measured best of {1,2,4} pairs x {4,5,6} CTAs
-// (4.76-5.45 ms at C2; more CTAs per SM spill).
+// Two pairs per vote and 4 CTAs per SM: measured best of {1,2,4} pairs x {3,4,5,6} CTAs (round 1: 4.76-5.45 ms at
+// C2; with the two-stage early reject 2.82 ms against 2.96-3.26 ms for the neighbours; more CTAs per SM spill).
 constexpr int K2P_PAIRS = 2;
+constexpr int K2P_CTAS = 4;
 
 template <bool EARLY>
-__global__ void __launch_bounds__(K2_THREADS, 4)
+__global__ void __launch_bounds__(K2_THREADS, K2P_CTAS)
 f_score_packed_kernel(const double *__restrict__ x1x2, int n, const double *__restrict__ Fall, int h,
                       double two_thr, int chunk, int32_t *__restrict__ counts) {
     extern __shared__ float4 spair[];  // chunk/2 pairs x 2 float4, pair-interleaved FP32 rows
@@ -498,7 +543,7 @@ static int f_score_launch(const double *d_x1x2, int32_t n, const double *d_F, in
     cudaStream_t st = as_stream(stream);
     SFM_CUDA_TRY(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)h, st));
     if (n == 0) return SFM_OK;
-    int chunk = all_fp64 ? pick_chunk(n, h) : pick_chunk_waves(n, h, 4);
+    int chunk = all_fp64 ? pick_chunk(n, h) : pick_chunk_waves(n, h, K2P_CTAS);
     dim3 grid(ceil_div(h, K2_THREADS), ceil_div(n, chunk));
     if (!all_fp64) {
         // development switch: the scalar-FP32 filter the packed kernel replaced
@@ -508,12 +553,15 @@ static int f_score_launch(const double *d_x1x2, int32_t n, const double *d_F, in
                 d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);
         else {
             // The early reject pays when whole warps certify their pairs as gross outliers: 97 % of the votes at
-            // the reference's 0.06 px (K2 at C2: 4.82 -> 3.97 ms), but a third to a half of them fail at 1.0 px and
-            // then the extra test costs (4.83 -> 5.18 ms; a per-warp adaptive switch lost on both: 4.20 / 5.04).
+            // the reference's 0.06 px (K2 at C2: 4.82 -> 3.97 ms with one stage, 2.82 ms with the two-stage form),
+            // but a third to a half of them fail at 1.0 px and then the extra test costs (4.83 -> 5.18 ms with one
+            // stage; a per-warp adaptive switch lost on both: 4.20 / 5.04). Two-stage form against the plain kernel's
+            // 4.82 ms (tools/k2_threshold_sweep.py, C2): 2.75 / 3.19 / 3.80 / 4.66 / 5.36 / 6.40 ms at
+            // 0.06 / 0.15 / 0.3 / 0.6 / 1.0 / 3.0 px -- the crossover sits near 0.65 px.
             // Thresholds are in pixels in the reference's domain, so the launch picks by threshold. Either kernel
             // gives the FP64 kernel's counts. SFM_F_SCORE_NO_EARLY / SFM_F_SCORE_EARLY force one of them.
             static const int forced = getenv("SFM_F_SCORE_NO_EARLY") ? 0 : getenv("SFM_F_SCORE_EARLY") ? 1 : -1;
-            const bool early = forced >= 0 ? forced == 1 : threshold < 0.3;
+            const bool early = forced >= 0 ? forced == 1 : threshold < 0.65;
             if (!early)
                 f_score_packed_kernel<false><<<grid, K2_THREADS, sizeof(float4) * (size_t)chunk, st>>>(
                     d_x1x2, n, d_F, h, 2.0 * threshold, chunk, d_counts);

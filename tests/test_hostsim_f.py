@@ -214,3 +214,30 @@ def test_early_reject_scales_and_degenerate_inputs():
         with np.errstate(all="ignore"):
             out = _reject(hs, r, f, thr)
         assert out[:, 1].sum() == 0
+
+
+def test_first_stage_of_the_early_reject_implies_the_full_certificate():
+    """K2 votes first on f_cert_reject_stage1 (one squared norm, no F^T x2). Whatever it rejects the full certificate
+    must reject too -- across noise levels, thresholds, scales of F and of the coordinates, and broken F -- and it
+    should catch most of what the full certificate catches."""
+    hs = hostsim.load()
+    rng = np.random.default_rng(24)
+
+    def stage1(rows, F, thr, chunk=1024):
+        out = np.zeros((len(F), 2), np.int64)
+        hs.hs_f_cert_stage1(_p(rows), len(rows), _p(np.ascontiguousarray(F)), len(F), C.c_double(thr), chunk, _p(out))
+        return out
+    rows = _two_view(rng, 1500, 0.3)
+    F = _hypotheses(hs, rows, rng, 200)
+    for thr in (0.06, 0.5, 3.0):
+        s1, full = stage1(rows, F, thr), _reject(hs, rows, F, thr)
+        assert s1[:, 1].sum() == 0
+        assert s1[:, 0].sum() <= full[:, 0].sum()
+        assert s1[:, 0].sum() > 0.95 * full[:, 0].sum()
+    Fbad = F[:8].copy()
+    Fbad[0, 3], Fbad[1, 8], Fbad[2] = np.nan, np.inf, 0.0
+    for r, f, thr in ((rows, F * 1e-25, 0.06), (rows, F * 1e25, 0.06), (np.ascontiguousarray(rows * 1e7), F, 0.06 * 1e7),
+                      (rows, Fbad, 0.06), (rows, F, 0.0), (rows, F, 1e6)):
+        with np.errstate(all="ignore"):
+            assert stage1(r, f, thr)[:, 1].sum() == 0
+
