@@ -35,7 +35,9 @@ def two_view(n=50_000, outlier_frac=0.30, noise=0.5, seed=20260102):
     x2[out_idx] = np.stack([rng.uniform(0, 800, n_out), rng.uniform(0, 600, n_out)], axis=1)
     is_outlier = np.zeros(n, bool)
     is_outlier[out_idx] = True
-    return dict(K=K_REF.copy(), X=X, x1=x1, x2=x2, R1=R1, C1=C1, R2=R2, C2=C2, is_outlier=is_outlier)
+    # C-contiguous, as np.array(list of matches) in the reference's wrapper gives (project() returns a transposed view)
+    return dict(K=K_REF.copy(), X=X, x1=np.ascontiguousarray(x1), x2=np.ascontiguousarray(x2), R1=R1, C1=C1, R2=R2, C2=C2,
+                is_outlier=is_outlier)
 
 
 def look_at(C, target):

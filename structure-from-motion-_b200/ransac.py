@@ -116,7 +116,7 @@ _PINNED: dict = {}
 STREAM_MIN_HYPOTHESES = 16384      # below this one sfm_f_ransac call is cheaper than chunking
 STREAM_CHUNKS = 2
 STREAM_FIRST_CHUNK = 4096
-STREAM_GROWTH = 2.0
+STREAM_GROWTH = 1.4
 
 
 def _side_stream() -> torch.cuda.Stream:
@@ -137,6 +137,18 @@ def _pinned_i32(rows: int, cols: int) -> torch.Tensor:
     return buf[:need].view(rows, cols)
 
 
+def _stream_buffers(n: int, h: int):
+    """Device buffers of f_ransac_stream, kept for the next call of the same shape on the same device (every
+    result leaves as a host copy, so nothing the caller holds aliases them)."""
+    k = (n, h, torch.cuda.current_device())
+    hit = _PINNED.get("stream_buffers")
+    if hit is None or hit[0] != k:
+        hit = (k, _alloc_result(n, h, False), device.empty((1,), torch.int64), device.empty((h, 8), torch.int32),
+               device.empty((2 * n, 2), torch.float64))
+        _PINNED["stream_buffers"] = hit
+    return hit[1:]
+
+
 def _pinned_f64(rows: int, cols: int) -> torch.Tensor:
     """Grow-only pinned staging buffer for the correspondences (a call ends with a synchronising read, so the
     buffer is free again when the next call fills it)."""
@@ -154,33 +166,31 @@ def f_ransac_stream(points1, points2, threshold, n_max, chunks=STREAM_CHUNKS):
     chunk (K1 + K2 per chunk, one K3 over all counts, K4 with the winner's row of F). The draws, their order and every result are the
     same as one sfm_f_ransac call over the whole stream. Returns the dict of f_ransac_host."""
     lib = _lib.load()
-    p1 = np.ascontiguousarray(points1, np.float64)
-    p2 = np.ascontiguousarray(points2, np.float64)
+    p1, p2 = np.asarray(points1), np.asarray(points2)
     n, h = len(p1), int(n_max)
     # [n,4] rows (x1,y1,x2,y2). Both point sets go through ONE pinned buffer (two contiguous host copies, one
     # asynchronous upload that overlaps the replay of the first chunk; a pageable source blocks the host for
     # ~0.7 ms at 50k correspondences) and are interleaved on the device
     pin_x = _pinned_f64(2 * n, 2)
     hx = pin_x.numpy()
-    np.copyto(hx[:n], p1)
-    np.copyto(hx[n:], p2)
-    d_pp = device.empty((2 * n, 2), torch.float64)
+    np.copyto(hx[:n], p1, casting="unsafe")           # one pass whatever the caller's dtype and strides
+    np.copyto(hx[n:], p2, casting="unsafe")
+    st = device.stream()
+    r, key, d_s, d_pp = _stream_buffers(n, h)
     d_pp.copy_(pin_x, non_blocking=True)
     d_x = torch.cat([d_pp[:n], d_pp[n:]], dim=1)
-    st = device.stream()
-    r = _alloc_result(n, h, False)
-    key = device.empty((1,), torch.int64)
-    d_s = device.empty((h, 8), torch.int32)
     pinned = _pinned_i32(h, 8)
     host = pinned.numpy()
     # chunk schedule: a small first chunk (the only one the GPU waits for), then growing by STREAM_GROWTH per
-    # chunk -- the replay runs ~2.2x faster than K2 scores (18 vs 40 ns per hypothesis on the B200 box), so the
-    # CPU stays ahead at a growth of 2 -- up to h / chunks (tools/fransac_e2e_trace.py prints the timeline)
+    # chunk -- the replay runs ~1.4x faster than K2 scores (18-22 vs 28 ns per hypothesis on the B200 box), so the
+    # CPU stays ahead at a growth of 1.4 -- up to h / chunks (tools/fransac_e2e_trace.py prints the timeline)
     big = max(1, -(-h // max(1, int(chunks))))
     sizes, c = [], min(big, STREAM_FIRST_CHUNK)
     while sum(sizes) < h:
         sizes.append(min(c, h - sum(sizes)))
         c = min(big, int(c * STREAM_GROWTH))
+    if len(sizes) > 1 and sizes[-1] < sizes[-2] // 3:       # no tiny last launch
+        sizes[-2] += sizes.pop()
     rep = sampler.StreamReplayer(n, 8)
     # the sample upload and K1 of chunk i+1 go to a side stream, so they overlap the tail of K2 of chunk i
     main = torch.cuda.current_stream()

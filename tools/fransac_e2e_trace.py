@@ -24,15 +24,14 @@ def traced():
     def mark(name):
         marks.append((name, time.perf_counter()))
     mark("start")
-    p1 = np.ascontiguousarray(sc["x1"], np.float64); p2 = np.ascontiguousarray(sc["x2"], np.float64)
+    p1 = np.asarray(sc["x1"]); p2 = np.asarray(sc["x2"])
     n, h = N, H
     pin_x = ransac._pinned_f64(2 * n, 2); hx = pin_x.numpy(); np.copyto(hx[:n], p1); np.copyto(hx[n:], p2)
     mark("points staged")
-    d_pp = device.empty((2 * n, 2), torch.float64); d_pp.copy_(pin_x, non_blocking=True)
-    d_x = torch.cat([d_pp[:n], d_pp[n:]], dim=1)
     st = device.stream()
-    r = ransac._alloc_result(n, h, False)
-    key = device.empty((1,), torch.int64); d_s = device.empty((h, 8), torch.int32)
+    r, key, d_s, d_pp = ransac._stream_buffers(n, h)
+    d_pp.copy_(pin_x, non_blocking=True)
+    d_x = torch.cat([d_pp[:n], d_pp[n:]], dim=1)
     pinned = ransac._pinned_i32(h, 8); host = pinned.numpy()
     mark("allocated")
     big = max(1, -(-h // 2)); sizes, c = [], min(big, ransac.STREAM_FIRST_CHUNK)
@@ -73,12 +72,12 @@ def traced():
 
 
 traced()
-for first, growth in [(3072, 2.5), (4096, 2.0), (6144, 2.0), (8192, 1.8), (8192, 2.2), (12288, 2.0)]:
+for first, growth in [(4096, 1.4), (2048, 1.4), (3072, 1.5), (4096, 1.3), (6144, 1.3)]:
     ransac.STREAM_FIRST_CHUNK, ransac.STREAM_GROWTH = first, growth
     ts = []
     for _ in range(8):
         t = time.perf_counter(); ransac.f_ransac_stream(sc["x1"], sc["x2"], T, H); ts.append(time.perf_counter() - t)
     print("first", first, "growth", growth, "ms min", round(1e3 * min(ts), 3), "median", round(1e3 * sorted(ts)[4], 3))
-ransac.STREAM_FIRST_CHUNK, ransac.STREAM_GROWTH = 8192, 2.0
+ransac.STREAM_FIRST_CHUNK, ransac.STREAM_GROWTH = 4096, 1.4
 print("----")
 traced()
