@@ -137,6 +137,20 @@ def _pinned_i32(rows: int, cols: int) -> torch.Tensor:
     return buf[:need].view(rows, cols)
 
 
+def _chunk_schedule(h: int, chunks: int = STREAM_CHUNKS) -> list:
+    """Chunk sizes of f_ransac_stream: STREAM_FIRST_CHUNK, then growing by STREAM_GROWTH up to h / chunks; a last
+    chunk under a third of its predecessor is merged into it (no tiny last launch). Sums to h."""
+    big = max(1, -(-h // max(1, int(chunks))))
+    sizes, c = [], min(big, STREAM_FIRST_CHUNK)
+    while sum(sizes) < h:
+        sizes.append(min(c, h - sum(sizes)))
+        c = min(big, max(c + 1, int(c * STREAM_GROWTH)))
+    if len(sizes) > 1 and sizes[-1] < sizes[-2] // 3:
+        last = sizes.pop()
+        sizes[-1] += last
+    return sizes
+
+
 def _stream_buffers(n: int, h: int):
     """Device buffers of f_ransac_stream, kept for the next call of the same shape on the same device (every
     result leaves as a host copy, so nothing the caller holds aliases them)."""
@@ -184,13 +198,7 @@ def f_ransac_stream(points1, points2, threshold, n_max, chunks=STREAM_CHUNKS):
     # chunk schedule: a small first chunk (the only one the GPU waits for), then growing by STREAM_GROWTH per
     # chunk -- the replay runs ~1.4x faster than K2 scores (18-22 vs 28 ns per hypothesis on the B200 box), so the
     # CPU stays ahead at a growth of 1.4 -- up to h / chunks (tools/fransac_e2e_trace.py prints the timeline)
-    big = max(1, -(-h // max(1, int(chunks))))
-    sizes, c = [], min(big, STREAM_FIRST_CHUNK)
-    while sum(sizes) < h:
-        sizes.append(min(c, h - sum(sizes)))
-        c = min(big, int(c * STREAM_GROWTH))
-    if len(sizes) > 1 and sizes[-1] < sizes[-2] // 3:       # no tiny last launch
-        sizes[-2] += sizes.pop()
+    sizes = _chunk_schedule(h, chunks)
     rep = sampler.StreamReplayer(n, 8)
     # the sample upload and K1 of chunk i+1 go to a side stream, so they overlap the tail of K2 of chunk i
     main = torch.cuda.current_stream()

@@ -122,3 +122,16 @@ def test_sample_stream_property_random_shapes():
         assert after_a == random.random(), (n, k, count, off)
 
     check()
+
+
+def test_stream_chunk_schedule_covers_the_stream():
+    """ransac.f_ransac_stream scores the hypotheses chunk by chunk: the chunk sizes must be positive, sum to the
+    stream length, never end on a sliver, and the first one stays small (the only one the GPU waits for)."""
+    from sfm_b200 import ransac
+    for h in (1, 2, 4095, 4096, 4097, 16384, 20000, 99999, 100000, 123457, 1000000):
+        for chunks in (1, 2, 3, 8):
+            s = ransac._chunk_schedule(h, chunks)
+            assert sum(s) == h and min(s) > 0, (h, chunks, s)
+            assert s[0] <= ransac.STREAM_FIRST_CHUNK + ransac.STREAM_FIRST_CHUNK // 3
+            if len(s) > 1:
+                assert s[-1] >= s[-2] // 4, (h, chunks, s)
