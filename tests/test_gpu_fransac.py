@@ -231,8 +231,10 @@ def test_certified_fp32_scoring_equals_fp64_kernel(cuda_device):
     xbad = x[:3001].copy()                      # odd count, non-finite coordinates in both pair lanes
     xbad[10, 0] = np.nan; xbad[11, 3] = np.inf; xbad[3000, 1] = np.nan; xbad[2048, 2] = -np.inf
     cases = [(x, 0.06), (x, 1.0), (np.floor(x), 0.06), (x * 1e-3, 1e-4), (x[:1237], 0.5), (x[:9], 0.5),
-             (x[:1025], 0.5), (x[:2050], 0.06), (x[:49999], 0.06), (xbad, 0.5), (xbad, 0.06), (x[:1237], 0.29)]
-    # thresholds below 0.3 px run the kernel with the sqrt-free early reject, the others the one without (f_ransac.cu)
+             (x[:1025], 0.5), (x[:2050], 0.06), (x[:49999], 0.06), (xbad, 0.5), (xbad, 0.06), (x[:1237], 0.29),
+             (x, 0.3), (x, 0.64), (x[:20001], 0.66), (x, 0.005), (np.floor(x), 0.5)]
+    # thresholds below 0.65 px run the kernel with the two-stage sqrt-free early reject, the others the one without
+    # (f_ransac.cu): both sides of the rule, tails of 1 .. 3 correspondences after the groups of 4, odd counts
     v = C.c_uint64(0)
     for rows, thr in cases:
         m = len(rows)
@@ -241,7 +243,7 @@ def test_certified_fp32_scoring_equals_fp64_kernel(cuda_device):
         d_F = torch.empty((h, 9), dtype=torch.float64, device="cuda")
         assert lib.sfm_f8pt_batch(d_x.data_ptr(), m, d_s.data_ptr(), h, d_F.data_ptr(), None) == 0
         variants = [d_F]
-        if m == n and thr == 0.06:
+        if m == n and thr in (0.06, 0.3):
             bad = d_F.clone()
             bad[0, 3] = float("nan"); bad[1, 8] = float("inf"); bad[2] = 0.0
             bad[3] *= 1e25; bad[4] *= 1e-25; bad[5] *= -1e8
