@@ -39,9 +39,9 @@ def measured_peaks():
 
 def _ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` at the bench shape, from the
-    committed ncu --set full capture (profiles/r01_ncu_traffic.json, written by tools/ncu_traffic.py)."""
+    committed ncu --set full capture (profiles/r02_ncu_traffic.json, written by tools/ncu_traffic.py)."""
     try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_ncu_traffic.json")) as f:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_ncu_traffic.json")) as f:
             return float(json.load(f)[kernel]["dram_bytes"])
     except Exception:
         return None
