@@ -25,9 +25,29 @@ namespace sfm {
 // ------------------------------------------------------------------------------------ K1
 __global__ void __launch_bounds__(128)
 f8pt_kernel(const double *__restrict__ x1x2, const int32_t *__restrict__ sample, int h,
-            double *__restrict__ Fout) {
+            double *__restrict__ Fout, const unsigned long long *__restrict__ key = nullptr,
+            int32_t *__restrict__ best = nullptr) {
     int hyp = blockIdx.x * blockDim.x + threadIdx.x;
-    if (hyp >= h) return;
+    double *out = Fout + (size_t)hyp * 9;
+    if (key) {
+        // multi-GPU tail (sfm_f_winner_from_key): the ONE hypothesis named by the all-reduced (count, ~index) key, F to
+        // Fout[0..9). The same kernel as the batch on purpose: the winner's F then has the bits a single GPU scoring
+        // the whole stream stores for it, whatever ptxas contracts.
+        if (hyp != 0) return;
+        const unsigned long long k = *key;
+        const int idx = (int)(0xFFFFFFFFu - (unsigned int)(k & 0xFFFFFFFFull)), cnt = (int)(k >> 32);
+        best[0] = idx;
+        best[1] = cnt;
+        if (cnt <= 0 || idx < 0 || idx >= h) {
+            best[1] = 0;
+            for (int i = 0; i < 9; ++i) Fout[i] = 0.0;
+            return;
+        }
+        hyp = idx;
+        out = Fout;
+    } else if (hyp >= h) {
+        return;
+    }
     double px1[8], py1[8], px2[8], py2[8];
     const int4 *sp = reinterpret_cast<const int4 *>(sample + (size_t)hyp * 8);
     int4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
@@ -41,7 +61,7 @@ f8pt_kernel(const double *__restrict__ x1x2, const int32_t *__restrict__ sample,
     double F[9];
     f8pt_from_sample(px1, py1, px2, py2, F);
 #pragma unroll
-    for (int i = 0; i < 9; ++i) Fout[(size_t)hyp * 9 + i] = F[i];
+    for (int i = 0; i < 9; ++i) out[i] = F[i];
 }
 
 // ------------------------------------------------------------------------------------ K2
@@ -649,30 +669,6 @@ extern "C" int sfm_f_ransac(const double *d_x1x2, int32_t n, const int32_t *d_sa
 // After the 8-byte max-allreduce of the packed key every rank decodes the global winner and
 // recomputes its F from the winning sample (all ranks hold the whole sample stream), so no
 // broadcast of F or of the mask is needed and all ranks end with identical bits.
-namespace sfm {
-__global__ void f_winner_from_key_kernel(const double *__restrict__ x1x2,
-                                         const int32_t *__restrict__ sample_all, int h_total,
-                                         const unsigned long long *__restrict__ key,
-                                         int32_t *__restrict__ best, double *__restrict__ Fbest) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    unsigned long long k = *key;
-    int idx = (int)(0xFFFFFFFFu - (unsigned int)(k & 0xFFFFFFFFull));
-    int cnt = (int)(k >> 32);
-    best[0] = idx;
-    best[1] = cnt;
-    if (cnt <= 0 || idx < 0 || idx >= h_total) {
-        best[1] = 0;
-        for (int i = 0; i < 9; ++i) Fbest[i] = 0.0;
-        return;
-    }
-    double px1[8], py1[8], px2[8], py2[8];
-    for (int i = 0; i < 8; ++i) {
-        const double *row = x1x2 + (size_t)sample_all[(size_t)idx * 8 + i] * 4;
-        px1[i] = row[0]; py1[i] = row[1]; px2[i] = row[2]; py2[i] = row[3];
-    }
-    f8pt_from_sample(px1, py1, px2, py2, Fbest);
-}
-}  // namespace sfm
 
 extern "C" int sfm_f_winner_from_key(const double *d_x1x2, int32_t n, const int32_t *d_sample_all,
                                      int32_t h_total, const uint64_t *d_key, double threshold,
@@ -680,9 +676,8 @@ extern "C" int sfm_f_winner_from_key(const double *d_x1x2, int32_t n, const int3
                                      double *d_err, void *stream) {
     if (!d_x1x2 || !d_sample_all || !d_key || !d_best || !d_Fbest || !d_mask || n < 8 || h_total < 1)
         return SFM_E_INVALID;
-    f_winner_from_key_kernel<<<1, 32, 0, as_stream(stream)>>>(
-        d_x1x2, d_sample_all, h_total, reinterpret_cast<const unsigned long long *>(d_key), d_best,
-        d_Fbest);
+    f8pt_kernel<<<1, 32, 0, as_stream(stream)>>>(d_x1x2, d_sample_all, h_total, d_Fbest,
+                                                 reinterpret_cast<const unsigned long long *>(d_key), d_best);
     SFM_LAUNCH_CHECK();
     // Fbase = d_Fbest, selected entry 0 (idx_offset = best[0]); valid iff best[1] > 0
     f_mask_kernel<<<ceil_div(n, 256), 256, 0, as_stream(stream)>>>(

@@ -59,6 +59,7 @@ def main():
         best = r.best.cpu().numpy()
         assert int(best[0]) == single["best_idx"] and int(best[1]) == single["best_count"], (best, single["best_idx"])
         assert np.array_equal(r.mask.cpu().numpy().astype(bool), single["mask"])
+        assert np.array_equal(r.F_best.cpu().numpy().reshape(3, 3), single["F_best"])     # the same bits as one GPU
     if rank == 0:
         print(f"F-RANSAC sharded winner {single['best_idx']} ({single['best_count']} inliers) on {world} GPUs: ok", flush=True)
     comm.destroy()

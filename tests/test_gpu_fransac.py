@@ -258,3 +258,25 @@ def test_certified_fp32_scoring_equals_fp64_kernel(cuda_device):
             assert torch.equal(a, b), (m, thr, int((a != b).sum()))
             if F is d_F and m == n:
                 assert v.value < 0.02 * m * h           # the filter decides almost everything
+
+
+def test_sharded_tail_reproduces_the_single_gpu_bits(cuda_device):
+    """The multi-GPU tail (sfm_f_winner_from_key) recomputes the winner's F from the winning sample on every rank:
+    it must give the bits the batch kernel stored for that hypothesis (world size 1, identity reduction, several
+    streams so that different winners are exercised)."""
+    from oracle import scenes
+    from sfm_b200 import device, ransac, sampler
+    n, h = 4000, 3000
+    for seed in range(6):
+        sc = scenes.two_view(n=n, seed=40 + seed)
+        random.seed(seed)
+        samples = sampler.sample_stream(n, 8, h)
+        d_x = device.to_device(np.ascontiguousarray(np.hstack([sc["x1"], sc["x2"]])))
+        d_s = device.to_device(samples, np.int32)
+        plan = ransac.FRansacPlan(n, h)
+        one = plan.run(d_x, d_s, 0.5)
+        F1, b1, m1 = one.F_best.cpu().numpy().copy(), one.best.cpu().numpy().copy(), one.mask.cpu().numpy().copy()
+        sh = plan.run_sharded(d_x, d_s, 0.5, 0, 1, all_reduce_max=lambda key: None)
+        assert np.array_equal(sh.best.cpu().numpy(), b1) and np.array_equal(sh.mask.cpu().numpy(), m1)
+        assert np.array_equal(sh.F_best.cpu().numpy(), F1), seed
+
