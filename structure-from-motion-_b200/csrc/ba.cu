@@ -668,6 +668,8 @@ ba_point_prep_kernel(const double *__restrict__ V, const double *__restrict__ gp
 //               on the diagonal) atomics per (slice, block) instead of per (point, pair).
 constexpr int SG_THREADS = 128;
 
+constexpr uint32_t SG_SELF = 0x80000000u;     // second word of a pair entry: bit 31 set = (o, o), bits 0..30 = the point
+
 __global__ void ba_pair_count_kernel(const int32_t *__restrict__ pt_ptr, const int32_t *__restrict__ cam_idx,
                                      int npts, unsigned long long *__restrict__ count) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -694,7 +696,9 @@ __global__ void ba_pair_emit_kernel(const int32_t *__restrict__ pt_ptr, const in
             // row observation = the one of the hi camera
             const int oi = ca >= cb ? o0 + a : o0 + b, oj = ca >= cb ? o0 + b : o0 + a;
             keys[w] = (uint32_t)hi * (uint32_t)nc + (uint32_t)lo;
-            pairs[w] = make_uint2((unsigned)oi, (unsigned)oj);
+            // an observation with itself (one per observation): the second word names the POINT instead (SG_SELF set),
+            // so that the gather can fetch h_p for the right-hand side without a dependent lookup
+            pairs[w] = make_uint2((unsigned)oi, a == b ? (SG_SELF | (unsigned)p) : (unsigned)oj);
             ++w;
             if (a != b && ca == cb) {
                 keys[w] = (uint32_t)hi * (uint32_t)nc + (uint32_t)lo;
@@ -792,7 +796,7 @@ __global__ void ba_pair_interleave_kernel(const uint32_t *__restrict__ keys, con
     keys_i[d] = ok ? keys[src] : SG_DEAD;
     // observation indices -> positions of their records in the camera-major Z array
     const uint2 pr = ok ? pairs[src] : make_uint2(0u, 0u);
-    pairs_i[d] = ok ? make_uint2((unsigned)zpos[pr.x], (unsigned)zpos[pr.y]) : make_uint2(0u, 0u);
+    pairs_i[d] = ok ? make_uint2((unsigned)zpos[pr.x], (pr.y & SG_SELF) ? pr.y : (unsigned)zpos[pr.y]) : make_uint2(0u, 0u);
 }
 
 // Lane = one slice of `seg` consecutive entries of the sorted list. The two 144-byte records of
@@ -802,8 +806,20 @@ __global__ void ba_pair_interleave_kernel(const uint32_t *__restrict__ keys, con
 // the indices run two entries ahead), and read back by their owner without bank conflicts
 // (record stride 9 x 16 B). The diagonal entries (o, o) -- one per observation, sorted by camera
 // -- also carry the reduced right-hand side g_red[c] -= Z_o h_p, which therefore needs no pass of
-// its own.
+// its own; their index word names the point (SG_SELF), and h_p is loaded one entry ahead like the
+// records (as a dependent lookup inside the iteration it put two memory latencies on every warp's
+// critical path: at least one lane of a warp holds such an entry in almost every iteration).
 constexpr size_t SG_SMEM = (size_t)(SG_THREADS / 32) * 2 * 2 * 32 * 9 * sizeof(double2);
+
+// the two record positions of a pair entry / h_p of a self entry (zero otherwise)
+__device__ __forceinline__ uint2 sg_records(uint2 e) { return make_uint2(e.x, (e.y & SG_SELF) ? e.x : e.y); }
+__device__ __forceinline__ void sg_load_h(const double *__restrict__ H, uint2 e, double (&h)[3]) {
+    h[0] = h[1] = h[2] = 0.0;
+    if (e.y & SG_SELF) {
+        const double *hp = H + 3 * (size_t)(e.y & ~SG_SELF);
+        h[0] = __ldg(hp); h[1] = __ldg(hp + 1); h[2] = __ldg(hp + 2);
+    }
+}
 
 __device__ __forceinline__ void sg_fetch(double2 *__restrict__ dst, const double2 *__restrict__ Z2, uint2 me, int lane) {
     // dst: [2][288] words of this warp and stage
@@ -837,15 +853,18 @@ ba_schur_gather_kernel(const uint32_t *__restrict__ keys, const uint2 *__restric
     uint32_t k_cur = kp[0], k_nx = seg > 1 ? kp[32] : SG_DEAD;
     uint2 me_cur = pp[0], me_nx = seg > 1 ? pp[32] : make_uint2(0u, 0u);
     uint32_t cur = k_cur;                                 // block being accumulated (SG_DEAD: nothing yet)
-    sg_fetch(wbuf, Z2, me_cur, lane);
+    sg_fetch(wbuf, Z2, sg_records(me_cur), lane);
+    double hn[3];
+    sg_load_h(H, me_cur, hn);
     for (int it = 0; it < seg; ++it) {
         const uint32_t k = k_cur;
-        const uint2 me = me_cur;
         k_cur = k_nx;
         me_cur = me_nx;
+        const double h[3] = {hn[0], hn[1], hn[2]};        // of this entry; the next entry's loads go out now
         if (it + 2 < seg) { k_nx = kp[(size_t)(it + 2) * 32]; me_nx = pp[(size_t)(it + 2) * 32]; }
         if (it + 1 < seg) {
-            sg_fetch(wbuf + ((it + 1) & 1) * (2 * 288), Z2, me_cur, lane);
+            sg_load_h(H, me_cur, hn);
+            sg_fetch(wbuf + ((it + 1) & 1) * (2 * 288), Z2, sg_records(me_cur), lane);
             asm volatile("cp.async.wait_group 1;" ::: "memory");
         } else {
             asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -863,11 +882,6 @@ ba_schur_gather_kernel(const uint32_t *__restrict__ keys, const uint2 *__restric
                 const double2 v = rj[i];
                 b[2 * i] = v.x;
                 b[2 * i + 1] = v.y;
-            }
-            double h[3] = {0.0, 0.0, 0.0};
-            if (me.x == me.y) {
-                const int p = pt_c[me.x];                 // me.x is a camera-major position
-                h[0] = H[3 * (size_t)p]; h[1] = H[3 * (size_t)p + 1]; h[2] = H[3 * (size_t)p + 2];
             }
 #pragma unroll
             for (int hh = 0; hh < 3; ++hh) {          // two rows of Z_i (three 16-byte words) at a time
