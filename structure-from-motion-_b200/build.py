@@ -64,7 +64,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
         src, obj = pair
         if not force and os.path.exists(obj) and os.path.getmtime(obj) >= hdr_m:
             return ""
-        cmd = [nvcc, *NVCC_FLAGS, "-x", "cu", "-c", src, "-o", obj]
+        # .cpp sources are host-only (the sample replay, the K11s planner): nvcc hands them to g++ as they are, so
+        # GCC attributes (function multiversioning in mt_sample.cpp) are seen by the compiler that implements them
+        lang = [] if src.endswith(".cpp") else ["-x", "cu"]
+        cmd = [nvcc, *NVCC_FLAGS, *lang, "-c", src, "-o", obj]
         p = subprocess.run(cmd, capture_output=True, text=True)
         if p.returncode != 0:
             raise RuntimeError(f"nvcc failed on {src}:\n{p.stdout}\n{p.stderr}")
