@@ -1,5 +1,5 @@
 """The rest of the hot path for __graft_entry__.smoke(): one small invocation each of triangulation,
-two-view pose, homography RANSAC and bundle adjustment on cuda:0, checked against the oracle.
+two-view pose, homography RANSAC, PnP RANSAC + NonlinearPnP and bundle adjustment on cuda:0, checked against the oracle.
 (Test infrastructure hook: it imports oracle/, so nothing in the product path may import it.)"""
 from __future__ import annotations
 
@@ -46,6 +46,18 @@ def run() -> str:
     hg = homography.h_ransac_host(p1, p2, hs, 5.0)
     hr = so.h_ransac_detailed(p1, p2, 5.0, hs)
     assert hg["best_idx"] == hr["best_idx"] and hg["best_count"] == hr["best_count"]
+    # K6a + K6 + K7: PnP RANSAC (LinearPnP hypotheses on the device) from the reference's RNG stream, then NonlinearPnP
+    from sfm_b200 import pnp_ransac
+    ps = scenes.pnp_scene(n=300, seed=17)
+    random.seed(5)
+    Cp, Rp = pnp_ransac.PnPRANSAC(ps["X"], ps["x"], scenes.K_REF, 200, 200)
+    random.seed(5)
+    Co, Ro = so.pnp_ransac(ps["X"], ps["x"], scenes.K_REF, 200, 200)
+    assert np.linalg.norm(Rp - Ro) < 1e-6 * np.linalg.norm(Ro) and np.linalg.norm(Cp - Co) <= 1e-6 * max(1.0, np.linalg.norm(Co))
+    Cn, Rn = refine.nonlinear_PnP(scenes.K_REF, Cp, Rp, ps["x"], ps["X"])
+    Cr, Rr = so.nonlinear_pnp(ps["X"], ps["x"], scenes.K_REF, Co, Ro)
+    pnp_cost = lambda C, R: 0.5 * float(np.sum(so.pnp_loss(so.pose_to_params(C, R), ps["X"], ps["x"], scenes.K_REF) ** 2))
+    assert abs(pnp_cost(Cn, Rn) - pnp_cost(Cr, Rr)) <= 1e-6 * pnp_cost(Cr, Rr)
     # K8..K12: a small bundle adjustment against scipy's 'lm' on the same residual
     from scipy.spatial.transform import Rotation
     bs = scenes.ba_scene(n_cams=5, n_pts=60, obs_per_pt=4, seed=13)
@@ -61,5 +73,5 @@ def run() -> str:
     assert rel < 1e-6, (cost, ref.cost)
     launches = _lib.launch_count() - before
     return (f"; triangulation, two-view pose ({tv['best_count']} in front), homography RANSAC "
-            f"({hg['best_count']} inliers), BA cost {cost:.6g} (rel. diff to scipy lm {rel:.1e}), "
+            f"({hg['best_count']} inliers), PnP RANSAC + NonlinearPnP (cost {pnp_cost(Cn, Rn):.5g}), BA cost {cost:.6g} (rel. diff to scipy lm {rel:.1e}), "
             f"{launches} more launches")
