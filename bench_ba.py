@@ -152,7 +152,7 @@ def run_single_gpu(args, peaks, peak_src, flush):
         e_its += info["n_linearisations"]
     dt = time.perf_counter() - t0
     out["e2e"] = {"value": e_its / dt, "unit": "LM iterations/s",
-                  "h2d_bytes_per_step": int(cams0.nbytes + pts0.nbytes + sc["obs"].nbytes + 8 * nobs),
+                  "h2d_bytes_per_step": int(cams0.nbytes + pts0.nbytes + sc["obs"].nbytes),   # the index arrays stay on the device (cache)
                   "d2h_bytes_per_step": int(cams0.nbytes + pts0.nbytes + 64),
                   "api": "sfm_b200.bundle.ba_solve_sparse(cams, pts, cam_idx, pt_idx, obs, K): host numpy in/out, "
                          "H2D of observations and parameters, solve, D2H every step; the per-problem preparation "
@@ -178,8 +178,24 @@ def run_single_gpu(args, peaks, peak_src, flush):
     d_c, d_p = device_copy(cams5), device_copy(pts5)
     prob5.solve_device(d_c, d_p, profile=True)
     c5_phases = bundle.last_profile()
+    # C5 end to end through the host-array API (the problem cache holds its own prepared problem after the first call)
+    prob5.close()
+    for _ in range(2):
+        bundle.ba_solve_sparse(cams5, pts5, sc5["cam_idx"], sc5["pt_idx"], sc5["obs"], sc5["K"])
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e5_its = 0
+    for _ in range(3):
+        _, _, i5 = bundle.ba_solve_sparse(cams5, pts5, sc5["cam_idx"], sc5["pt_idx"], sc5["obs"], sc5["K"])
+        e5_its += i5["n_linearisations"]
+    dt5 = time.perf_counter() - t0
+    c5_e2e = {"value": e5_its / dt5, "unit": "LM iterations/s", "ms_per_call": dt5 / 3 * 1e3, "steps": 3,
+              "h2d_bytes_per_step": int(cams5.nbytes + pts5.nbytes + sc5["obs"].nbytes),
+              "d2h_bytes_per_step": int(cams5.nbytes + pts5.nbytes + 64),
+              "api": "sfm_b200.bundle.ba_solve_sparse, host numpy in/out"}
+    bundle.clear_problem_cache()
     k9 = passes["K9p ba_point_pass_kernel"]
-    out["c5_single_gpu"] = {"workload": "C5 synthetic BAL-scale BA on ONE GPU: " + _name(C5),
+    out["c5_single_gpu"] = {"e2e": c5_e2e, "workload": "C5 synthetic BAL-scale BA on ONE GPU: " + _name(C5),
                             "value": its5 / (ms5 * 1e-3), "unit": "LM iterations/s", "ms_per_solve": ms5 / 3,
                             "lm_iterations_per_solve": its5 / 3, "cost": infos5[-1]["cost"],
                             "rmse_px": float(np.sqrt(2 * infos5[-1]["cost"] / n5)), "passes": passes,
