@@ -98,8 +98,7 @@ class BAProblem:
         # half as fast (3.2 MB at C3)
         if getattr(self, "_pin_obs", None) is None:
             self._pin_obs = torch.empty((self.n_obs, 2), dtype=torch.float64, pin_memory=True)
-        self._pin_obs.numpy()[...] = obs
-        self.d_obs.copy_(self._pin_obs, non_blocking=True)
+        device.upload_via_pinned(self.d_obs, obs, self._pin_obs)
         if K is not None:
             self.K = np.ascontiguousarray(K, np.float64).reshape(3, 3)
 
@@ -194,7 +193,7 @@ def _cached_problem(n_cams, n_pts, cam_idx, pt_idx, obs, K):
     if key is None:
         key = (int(n_cams), int(n_pts), len(cam_idx), zlib.crc32(cam_idx), zlib.crc32(pt_idx), dev)
     prob = _PROBLEMS.pop(key, None)
-    if prob is not None and not (np.array_equal(prob._key_cam, cam_idx) and np.array_equal(prob._key_pt, pt_idx)):
+    if prob is not None and not (device.arrays_equal(prob._key_cam, cam_idx) and device.arrays_equal(prob._key_pt, pt_idx)):
         prob.close()                                  # changed in place, or a checksum collision: not the same tracks
         prob = None
         key = (int(n_cams), int(n_pts), len(cam_idx), zlib.crc32(cam_idx), zlib.crc32(pt_idx), dev)
@@ -216,7 +215,14 @@ def ba_solve_sparse(cams, pts, cam_idx, pt_idx, obs, K, max_nfev=BA_MAX_NFEV, to
     cams = np.ascontiguousarray(cams, np.float64).reshape(-1, 6)
     pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 3)
     prob = _cached_problem(len(cams), len(pts), cam_idx, pt_idx, obs, K)
-    d_cam, d_pts = device.to_device(cams), device.to_device(pts)
+    d_cam = device.to_device(cams)
+    if pts.nbytes >= device.PAR_MIN_BYTES:                 # a large point set goes up like the observations do
+        if getattr(prob, "_pin_pts", None) is None:
+            prob._pin_pts = torch.empty(pts.shape, dtype=torch.float64, pin_memory=True)
+        d_pts = device.empty(pts.shape, torch.float64)
+        device.upload_via_pinned(d_pts, pts, prob._pin_pts)
+    else:
+        d_pts = device.to_device(pts)
     info = prob.solve_device(d_cam, d_pts, max_nfev, tol, verbose=verbose)
     return d_cam.cpu().numpy(), d_pts.cpu().numpy(), info
 
