@@ -215,16 +215,26 @@ def ba_solve_sparse(cams, pts, cam_idx, pt_idx, obs, K, max_nfev=BA_MAX_NFEV, to
     cams = np.ascontiguousarray(cams, np.float64).reshape(-1, 6)
     pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 3)
     prob = _cached_problem(len(cams), len(pts), cam_idx, pt_idx, obs, K)
-    d_cam = device.to_device(cams)
-    if pts.nbytes >= device.PAR_MIN_BYTES:                 # a large point set goes up like the observations do
-        if getattr(prob, "_pin_pts", None) is None:
-            prob._pin_pts = torch.empty(pts.shape, dtype=torch.float64, pin_memory=True)
-        d_pts = device.empty(pts.shape, torch.float64)
-        device.upload_via_pinned(d_pts, pts, prob._pin_pts)
+    # parameters travel as ONE pinned buffer [cameras | points] each way: one asynchronous upload, one download and
+    # one synchronisation per call (two pageable copies each way cost ~0.1 ms of a 1.5 ms call at C3)
+    nc6, np3 = cams.size, pts.size
+    if getattr(prob, "_pin_par", None) is None or prob._pin_par.numel() != nc6 + np3:
+        prob._pin_par = torch.empty(nc6 + np3, dtype=torch.float64, pin_memory=True)
+        prob._d_par = device.empty((nc6 + np3,), torch.float64)
+    hp = prob._pin_par.numpy()
+    d_par = prob._d_par
+    np.copyto(hp[:nc6], cams.reshape(-1))
+    if pts.nbytes >= device.PAR_MIN_BYTES:
+        device.upload_via_pinned(d_par[nc6:], pts.reshape(-1), prob._pin_par[nc6:])
+        d_par[:nc6].copy_(prob._pin_par[:nc6], non_blocking=True)
     else:
-        d_pts = device.to_device(pts)
-    info = prob.solve_device(d_cam, d_pts, max_nfev, tol, verbose=verbose)
-    return d_cam.cpu().numpy(), d_pts.cpu().numpy(), info
+        np.copyto(hp[nc6:], pts.reshape(-1))
+        d_par.copy_(prob._pin_par, non_blocking=True)
+    d_cam, d_pts = d_par[:nc6].view(-1, 6), d_par[nc6:].view(-1, 3)
+    info = prob.solve_device(d_cam, d_pts, max_nfev, tol, verbose=verbose)        # ends with a stream synchronisation
+    prob._pin_par.copy_(d_par, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return hp[:nc6].reshape(-1, 6).copy(), hp[nc6:].reshape(-1, 3).copy(), info
 
 
 # ---------------------------------------------------------------------------------------------
