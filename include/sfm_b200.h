@@ -82,6 +82,12 @@ int sfm_f_score_fp64_tests(uint64_t *out, int32_t reset);
 int sfm_argmax_first(const int32_t *d_counts, int32_t h, int32_t idx_offset, int32_t *d_best,
                      uint64_t *d_key, void *stream);
 
+/* K3 for many consecutive RANSAC runs in one launch: segment b = d_counts[b * seg_len .. (b+1) * seg_len),
+ * d_best[2b] = first index (within the segment) with the segment's maximum count, d_best[2b+1] = that count --
+ * the result of n_seg calls of sfm_argmax_first (PnPRANSAC.py:72 once per registration). */
+int sfm_argmax_first_batch(const int32_t *d_counts, int32_t n_seg, int32_t seg_len, int32_t *d_best,
+                           void *stream);
+
 /* K4: inlier mask + per-point error for ONE fundamental matrix d_Fone[9]
  * (GetInliersRANSAC.py:67-81). d_mask [n] uint8, d_err [n] float64 (may be null). */
 int sfm_f_inlier_mask(const double *d_x1x2, int32_t n, const double *d_Fone, double threshold,
@@ -153,6 +159,14 @@ int sfm_nltri(const double *h_P1, const double *h_P2, const double *d_x1, const 
  * sfm_argmax_first for the strict-'>' first-maximum rule (PnPRANSAC.py:72). */
 int sfm_pnp_score_count(const double *d_P, const double *d_X, const double *d_x, int32_t n,
                         int32_t h, double threshold, int32_t *d_counts, void *stream);
+
+/* K6 for n_regs registrations in one launch (PnPRANSAC.py:59-69 once per registration, BASELINE config 4):
+ * registration b owns rows d_offsets[b] .. d_offsets[b+1]-1 of d_X [M,3] / d_x [M,2] (max_n = the longest),
+ * hypotheses d_P[b * h_per_reg .. ) and counts d_counts[b * h_per_reg .. ) (overwritten). The same kernel and the
+ * same arithmetic as sfm_pnp_score_count, so the counts equal those of n_regs separate calls. */
+int sfm_pnp_score_count_batch(const double *d_P, const double *d_X, const double *d_x,
+                              const int32_t *d_offsets, int32_t n_regs, int32_t max_n, int32_t h_per_reg,
+                              double threshold, int32_t *d_counts, void *stream);
 
 /* K7: NonLinearPnP (NonlinearPnP.py:47-123) for a batch of independent registrations.
  * h_K: HOST 3x3 intrinsics. Problem b uses rows d_offsets[b]..d_offsets[b+1]-1 of d_X [M,3] /

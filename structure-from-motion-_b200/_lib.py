@@ -31,6 +31,9 @@ SIGNATURES = {
     "sfm_f_score_count_fp64": (C.c_int, [c_f64p, C.c_int32, c_f64p, C.c_int32, C.c_double, c_i32p, c_vp]),
     "sfm_f_score_fp64_tests": (C.c_int, [C.POINTER(C.c_uint64), C.c_int32]),
     "sfm_argmax_first": (C.c_int, [c_i32p, C.c_int32, C.c_int32, c_i32p, c_vp, c_vp]),
+    "sfm_argmax_first_batch": (C.c_int, [c_i32p, C.c_int32, C.c_int32, c_i32p, c_vp]),
+    "sfm_pnp_score_count_batch": (C.c_int, [c_f64p, c_f64p, c_f64p, c_i32p, C.c_int32, C.c_int32, C.c_int32, C.c_double,
+                                            c_i32p, c_vp]),
     "sfm_f_inlier_mask": (C.c_int, [c_f64p, C.c_int32, c_f64p, C.c_double, c_u8p, c_f64p, c_vp]),
     "sfm_f_ransac": (C.c_int, [c_f64p, C.c_int32, c_i32p, C.c_int32, C.c_double, c_f64p, c_i32p,
                                c_i32p, c_f64p, c_u8p, c_f64p, c_vp]),

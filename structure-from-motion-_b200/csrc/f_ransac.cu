@@ -470,6 +470,10 @@ __global__ void __launch_bounds__(1024)
 argmax_first_kernel(const int32_t *__restrict__ counts, int h, int idx_offset,
                     int32_t *__restrict__ best, unsigned long long *__restrict__ key_out) {
     __shared__ unsigned long long swarp[32];
+    // one block per segment of h counts (sfm_argmax_first_batch; a single block for sfm_argmax_first)
+    counts += (size_t)blockIdx.x * h;
+    best += 2 * (size_t)blockIdx.x;
+    if (key_out) key_out += blockIdx.x;
     unsigned long long k = 0ull;  // count 0 at "index 0xFFFFFFFF": loses to any real entry
     for (int i = threadIdx.x; i < h; i += blockDim.x) {
         unsigned long long c = (unsigned long long)(unsigned int)max(counts[i], 0);
@@ -635,6 +639,15 @@ extern "C" int sfm_argmax_first(const int32_t *d_counts, int32_t h, int32_t idx_
     if (!d_counts || !d_best || h < 0) return SFM_E_INVALID;
     argmax_first_kernel<<<1, 1024, 0, as_stream(stream)>>>(
         d_counts, h, idx_offset, d_best, reinterpret_cast<unsigned long long *>(d_key));
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+extern "C" int sfm_argmax_first_batch(const int32_t *d_counts, int32_t n_seg, int32_t seg_len, int32_t *d_best,
+                                      void *stream) {
+    if (!d_counts || !d_best || n_seg < 0 || seg_len < 0) return SFM_E_INVALID;
+    if (n_seg == 0) return SFM_OK;
+    argmax_first_kernel<<<n_seg, 256, 0, as_stream(stream)>>>(d_counts, seg_len, 0, d_best, nullptr);
     SFM_LAUNCH_CHECK();
     return SFM_OK;
 }

@@ -165,10 +165,21 @@ constexpr int K6_CHUNK = 512;
 
 __global__ void __launch_bounds__(K6_THREADS)
 pnp_score_kernel(const double *__restrict__ Pall, const double *__restrict__ X,
-                 const double *__restrict__ x, int n, int h, double thr, int32_t *__restrict__ counts) {
+                 const double *__restrict__ x, int n, int h, double thr, int32_t *__restrict__ counts,
+                 const int32_t *__restrict__ offsets = nullptr) {
     __shared__ double sX[K6_CHUNK * 3];
     __shared__ double sx[K6_CHUNK * 2];
+    if (offsets) {
+        // batched form (sfm_pnp_score_count_batch): blockIdx.z = registration, its rows, hypotheses and counts
+        const int b = blockIdx.z, o = offsets[b];
+        n = offsets[b + 1] - o;
+        X += 3 * (size_t)o;
+        x += 2 * (size_t)o;
+        Pall += (size_t)b * h * 12;
+        counts += (size_t)b * h;
+    }
     const int p0 = blockIdx.y * K6_CHUNK;
+    if (p0 >= n) return;                                   // block-uniform: before any barrier
     const int np = min(K6_CHUNK, n - p0);
     for (int i = threadIdx.x; i < np * 3; i += K6_THREADS) sX[i] = X[3 * (size_t)p0 + i];
     for (int i = threadIdx.x; i < np * 2; i += K6_THREADS) sx[i] = x[2 * (size_t)p0 + i];
@@ -213,6 +224,21 @@ extern "C" int sfm_pnp_score_count(const double *d_P, const double *d_X, const d
     if (n == 0) return SFM_OK;
     dim3 grid(ceil_div(h, K6_THREADS), ceil_div(n, K6_CHUNK));
     pnp_score_kernel<<<grid, K6_THREADS, 0, st>>>(d_P, d_X, d_x, n, h, threshold, d_counts);
+    SFM_LAUNCH_CHECK();
+    return SFM_OK;
+}
+
+extern "C" int sfm_pnp_score_count_batch(const double *d_P, const double *d_X, const double *d_x,
+                                         const int32_t *d_offsets, int32_t n_regs, int32_t max_n, int32_t h_per_reg,
+                                         double threshold, int32_t *d_counts, void *stream) {
+    if (!d_P || !d_X || !d_x || !d_offsets || !d_counts || n_regs < 0 || max_n < 0 || h_per_reg < 0) return SFM_E_INVALID;
+    if (n_regs == 0 || h_per_reg == 0) return SFM_OK;
+    if (n_regs > 65535) return SFM_E_INVALID;             // gridDim.z
+    cudaStream_t st = as_stream(stream);
+    SFM_CUDA_TRY(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)n_regs * h_per_reg, st));
+    if (max_n == 0) return SFM_OK;
+    dim3 grid(ceil_div(h_per_reg, K6_THREADS), ceil_div(max_n, K6_CHUNK), n_regs);
+    pnp_score_kernel<<<grid, K6_THREADS, 0, st>>>(d_P, d_X, d_x, 0, h_per_reg, threshold, d_counts, d_offsets);
     SFM_LAUNCH_CHECK();
     return SFM_OK;
 }

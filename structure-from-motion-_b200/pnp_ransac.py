@@ -115,8 +115,8 @@ def PnPRANSAC(X, x, K, threshold=200, n_max=1000, info=None):
 def pnp_ransac_batch(X_list, x_list, K, threshold=200, n_max=1000):
     """Many registrations at once (BASELINE config 4: 500 x 2,000 correspondences x 1,000 hypotheses): the sample
     streams are drawn registration after registration from the global `random` stream exactly as consecutive
-    PnPRANSAC calls would, ONE hypothesis launch covers all registrations, scoring + argmax run per registration on
-    slices, one D2H brings all winners back. Returns (C [B,3], R [B,3,3], counts [B]). Registrations whose best
+    PnPRANSAC calls would (one replayer: the generator state is read and written back once), ONE launch each for the
+    hypotheses, the scoring and the argmax of all registrations, one D2H brings all winners back. Returns (C [B,3], R [B,3,3], counts [B]). Registrations whose best
     count is below 4 fall back to LinearPnP on all their points (PnPRANSAC.py:82-87)."""
     B = len(X_list)
     sizes = [len(X) for X in X_list]
@@ -125,17 +125,27 @@ def pnp_ransac_batch(X_list, x_list, K, threshold=200, n_max=1000):
     offs = np.zeros(B + 1, np.int32)
     offs[1:] = np.cumsum(sizes)
     samples = np.empty((B * n_max, 4), np.int32)
-    for b in range(B):
-        sampler.sample_stream(sizes[b], 4, int(n_max), out=samples[b * n_max:(b + 1) * n_max])
+    rep = sampler.StreamReplayer(min(sizes), 4)           # ONE read and ONE write-back of the generator state
+    try:
+        for b in range(B):
+            rep.draw(int(n_max), samples[b * n_max:(b + 1) * n_max], n=sizes[b])
+    finally:
+        rep.finish()
     d_X = device.to_device(np.concatenate([np.asarray(X, np.float64) for X in X_list]))
     d_x = device.to_device(np.concatenate([np.asarray(x, np.float64) for x in x_list]))
     d_off = device.to_device(offs, np.int32)
     d_C, d_R, d_P, _ = linear_pnp4_device(d_X, d_x, device.to_device(samples, np.int32), K, d_off, B)
     d_counts = device.empty((B * n_max,), torch.int32)
     d_best = device.empty((B, 2), torch.int32)
-    for b in range(B):
-        pnp_score_device(d_P[b * n_max:(b + 1) * n_max], d_X[offs[b]:offs[b + 1]], d_x[offs[b]:offs[b + 1]], threshold,
-                         d_counts[b * n_max:(b + 1) * n_max], d_best[b])
+    lib, st = _lib.load(), device.stream()
+    for b0 in range(0, B, 65535):                                  # gridDim.z
+        nb = min(65535, B - b0)
+        _lib.check(lib.sfm_pnp_score_count_batch(device.ptr(d_P) + 96 * b0 * n_max, device.ptr(d_X), device.ptr(d_x),
+                                                 device.ptr(d_off) + 4 * b0, nb, int(max(sizes[b0:b0 + nb])), int(n_max),
+                                                 float(threshold), device.ptr(d_counts) + 4 * b0 * n_max, st),
+                   "sfm_pnp_score_count_batch")
+    _lib.check(lib.sfm_argmax_first_batch(device.ptr(d_counts), B, int(n_max), device.ptr(d_best), st),
+               "sfm_argmax_first_batch")
     w = d_best[:, 0].long() + torch.arange(B, device=d_best.device) * n_max
     packed = torch.cat([d_best[:, 1:2].double(), d_C.index_select(0, w), d_R.index_select(0, w)], dim=1).cpu().numpy()
     counts = packed[:, 0].astype(np.int64)

@@ -46,7 +46,7 @@ def sample_stream(n: int, k: int, count: int, out: np.ndarray | None = None) -> 
         out = np.empty((count, k), dtype=np.int32)
     rc = _lib.load().sfm_mt_sample_stream(mt.ctypes.data, C.addressof(idx), n, k, count, out.ctypes.data)
     _lib.check(rc, "sfm_mt_sample_stream")
-    random.setstate((3, tuple(int(v) for v in mt) + (int(idx.value),), st[2]))
+    random.setstate((3, tuple(mt.tolist()) + (int(idx.value),), st[2]))
     return out
 
 
@@ -70,16 +70,20 @@ class StreamReplayer:
             self._idx = C.c_int32(st[1][624])
             self._fn = _lib.load().sfm_mt_sample_stream
 
-    def draw(self, count: int, out: np.ndarray) -> np.ndarray:
-        """Fill out [count, k] (C-contiguous int32) with the next `count` index sets."""
+    def draw(self, count: int, out: np.ndarray, n: int | None = None) -> np.ndarray:
+        """Fill out [count, k] (C-contiguous int32) with the next `count` index sets. n: draw from range(n) instead
+        of the replayer's own population (consecutive registrations of different sizes on ONE stream; n >= k)."""
+        n = self.n if n is None else int(n)
+        if n < self.k or n >= 2 ** 31:
+            raise ValueError("StreamReplayer.draw: the population must hold at least k and fewer than 2^31 elements")
         if out.shape != (count, self.k) or out.dtype != np.int32 or not out.flags.c_contiguous:
             raise ValueError("out must be a C-contiguous int32 array of shape (count, min(k, n))")
         if count <= 0:
             return out
         if not self.fast:
-            out[...] = _python_stream(self.n, self.k, count)
+            out[...] = _python_stream(n, self.k, count)
             return out
-        rc = self._fn(self._mt.ctypes.data, C.addressof(self._idx), self.n, self.k, count, out.ctypes.data)
+        rc = self._fn(self._mt.ctypes.data, C.addressof(self._idx), n, self.k, count, out.ctypes.data)
         _lib.check(rc, "sfm_mt_sample_stream")
         return out
 

@@ -5,6 +5,7 @@ import random
 import re
 
 import numpy as np
+import pytest
 
 from conftest import ROOT
 from sfm_b200 import _lib, sampler
@@ -135,3 +136,31 @@ def test_stream_chunk_schedule_covers_the_stream():
             assert s[0] <= ransac.STREAM_FIRST_CHUNK + ransac.STREAM_FIRST_CHUNK // 3
             if len(s) > 1:
                 assert s[-1] >= s[-2] // 4, (h, chunks, s)
+
+
+def test_stream_replayer_with_a_population_per_draw():
+    """pnp_ransac_batch replays the samples of consecutive registrations of DIFFERENT sizes with one replayer
+    (StreamReplayer.draw(..., n=...)): the draws and the generator state afterwards must equal those of the
+    reference's consecutive random.sample calls, including the pool branch of random.sample (n <= 21)."""
+    import random
+    from sfm_b200 import sampler
+    sizes = [300, 2000, 97, 50000, 5, 4, 21, 22]
+    random.seed(9)
+    ref = [np.array([random.sample(range(n), 4) for _ in range(60)]) for n in sizes]
+    after = random.random()
+    random.seed(9)
+    rep = sampler.StreamReplayer(min(sizes), 4)
+    outs = []
+    for n in sizes:
+        o = np.empty((60, 4), np.int32)
+        rep.draw(60, o, n=n)
+        outs.append(o)
+    rep.finish()
+    assert random.random() == after
+    assert all(np.array_equal(a, b) for a, b in zip(ref, outs))
+    rep = sampler.StreamReplayer(10, 4)
+    try:
+        with pytest.raises(ValueError):
+            rep.draw(1, np.empty((1, 4), np.int32), n=3)
+    finally:
+        rep.finish()

@@ -164,3 +164,37 @@ def test_pnp_ransac_falls_back_to_all_points(cuda_device):
     with redirect_stdout(io.StringIO()):
         C0, R0 = pnp_ransac.PnPRANSAC(X, x, K, threshold=200, n_max=0)          # no iterations at all: same fallback
     assert np.array_equal(C0, Ca)
+
+
+def test_batched_scoring_and_argmax_equal_the_per_registration_calls(cuda_device):
+    """sfm_pnp_score_count_batch / sfm_argmax_first_batch (one launch for all registrations of a batch) against
+    sfm_pnp_score_count + sfm_argmax_first per registration: ragged sizes around the 512-row chunk, a registration
+    without any inlier, hypothesis counts that are not a multiple of the block."""
+    import torch
+    from oracle import scenes
+    from sfm_b200 import _lib, device, pnp_ransac
+    lib = _lib.load()
+    sizes = [4, 511, 512, 513, 37, 2000, 1025]
+    h = 300
+    regs = [scenes.pnp_scene(n=max(n, 8), seed=70 + i) for i, n in enumerate(sizes)]
+    Xs = [r["X"][:n] for r, n in zip(regs, sizes)]
+    xs = [r["x"][:n].copy() for r, n in zip(regs, sizes)]
+    xs[4] += 1e6                                                     # nothing reprojects within the threshold
+    offs = np.zeros(len(sizes) + 1, np.int32)
+    offs[1:] = np.cumsum(sizes)
+    rng = np.random.default_rng(3)
+    samples = np.concatenate([np.stack([rng.choice(n, 4, replace=False) for _ in range(h)]) for n in sizes]).astype(np.int32)
+    d_X, d_x = device.to_device(np.concatenate(Xs)), device.to_device(np.concatenate(xs))
+    d_off = device.to_device(offs, np.int32)
+    _, _, d_P, _ = pnp_ransac.linear_pnp4_device(d_X, d_x, device.to_device(samples, np.int32), scenes.K_REF, d_off, len(sizes))
+    d_counts = device.empty((len(sizes) * h,), torch.int32)
+    d_best = device.empty((len(sizes), 2), torch.int32)
+    _lib.check(lib.sfm_pnp_score_count_batch(device.ptr(d_P), device.ptr(d_X), device.ptr(d_x), device.ptr(d_off),
+                                             len(sizes), max(sizes), h, 200.0, device.ptr(d_counts), device.stream()), "batch")
+    _lib.check(lib.sfm_argmax_first_batch(device.ptr(d_counts), len(sizes), h, device.ptr(d_best), device.stream()), "argmax")
+    counts, best = d_counts.cpu().numpy().reshape(len(sizes), h), d_best.cpu().numpy()
+    for b, n in enumerate(sizes):
+        c1, b1 = pnp_ransac.pnp_score_device(d_P[b * h:(b + 1) * h], d_X[offs[b]:offs[b + 1]], d_x[offs[b]:offs[b + 1]], 200.0)
+        assert np.array_equal(counts[b], c1.cpu().numpy()), b
+        assert np.array_equal(best[b], b1.cpu().numpy()), b
+    assert best[4, 1] == 0 and counts[5].max() > 1500
