@@ -62,6 +62,23 @@ def main():
         assert np.array_equal(r.F_best.cpu().numpy().reshape(3, 3), single["F_best"])     # the same bits as one GPU
     if rank == 0:
         print(f"F-RANSAC sharded winner {single['best_idx']} ({single['best_count']} inliers) on {world} GPUs: ok", flush=True)
+    # ---- independent problems (second row): chunks per rank + all-gather == the single-GPU call ----
+    from sfm_b200 import refine, shard
+    tv = scenes.two_view(n=2001, outlier_frac=0.0, seed=21)
+    args = (tv["K"], tv["C1"], tv["R1"], tv["C2"], tv["R2"], tv["x1"], tv["x2"])
+    X0 = shard.linear_triangulation_sharded(*args)
+    assert np.array_equal(X0, refine.LinearTriangulation(*args))
+    X = shard.nonlinear_triangulation_sharded(*args, X0)
+    assert np.array_equal(X, refine.NonLinearTriangulation(*args, X0))
+    regs = [scenes.pnp_scene(n=200 + 10 * b, outlier_frac=0.0, seed=300 + b) for b in range(7)]
+    Xs, xs = [r["X"] for r in regs], [r["x"] for r in regs]
+    C0 = [r["C"] + 0.05 for r in regs]
+    R0 = [r["R"] for r in regs]
+    Cs, Rs = shard.nonlinear_pnp_sharded(Xs, xs, scenes.K_REF, C0, R0)
+    C1, R1, _ = refine.nonlinear_pnp_batch(Xs, xs, scenes.K_REF, C0, R0)
+    assert np.array_equal(Cs, np.array(C1)) and np.array_equal(Rs, np.array(R1))
+    if rank == 0:
+        print(f"sharded triangulation (2001 points) and NonLinearPnP (7 registrations) on {world} GPUs: bit-equal to one GPU", flush=True)
     comm.destroy()
     dist.destroy_process_group()
 

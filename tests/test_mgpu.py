@@ -65,6 +65,66 @@ def _gloo_worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
+def test_shard_range_is_a_balanced_partition():
+    from sfm_b200.shard import shard_range
+    for n in (0, 1, 2, 7, 8, 1000, 1_000_003):
+        for world in (1, 2, 3, 8):
+            r = [shard_range(n, k, world) for k in range(world)]
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(r[:-1], r[1:]))
+            sizes = [b - a for a, b in r]
+            assert max(sizes) - min(sizes) <= 1 and sizes == sorted(sizes, reverse=True)
+    with pytest.raises(ValueError):
+        shard_range(5, 2, 2)
+
+
+def _gloo_map_worker(rank, world, port, q):
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    from sfm_b200.shard import map_sharded, shard_range
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(3)
+        for n in (11, 2, 1, 0, 1000):                                    # odd split, fewer problems than ranks, none
+            a, b = rng.normal(size=(n, 2)), rng.normal(size=(n, 3))
+            seen = []
+
+            def fn(x, y):
+                seen.append(len(x))
+                return np.hstack([2.0 * x, y - 1.0, (x[:, :1] * y[:, :1])])
+            out = map_sharded(fn, n, (a, b))
+            lo, hi = shard_range(n, rank, world)
+            assert seen == ([hi - lo] if hi > lo else [])                 # only this rank's chunk was computed here
+            if n:
+                assert out.shape == (n, 6) and np.array_equal(out, np.hstack([2.0 * a, b - 1.0, a[:, :1] * b[:, :1]]))
+            else:
+                assert out.shape[0] == 0
+        out = map_sharded(lambda x: np.einsum("ni,nj->nij", x, x), 5, (np.arange(15.0).reshape(5, 3),))   # trailing shape (3,3)
+        assert out.shape == (5, 3, 3) and out[4, 2, 2] == 14.0 ** 2
+        q.put((rank, "ok"))
+    except Exception as e:                                                # noqa: BLE001
+        q.put((rank, repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_independent_problems_are_chunked_and_gathered():
+    """SURVEY 8e, second row: per-point / per-registration solvers shard as contiguous chunks with an all-gather of
+    the results -- the plumbing (sfm_b200.shard.map_sharded) on two gloo ranks with a stand-in for the kernel."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + os.getpid() % 200
+    procs = [ctx.Process(target=_gloo_map_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, "ok"), (1, "ok")], res
+
+
 def test_gloo_world2_plumbing():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
