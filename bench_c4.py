@@ -101,7 +101,7 @@ def run(flush=None, with_cpu=True):
     import random
     from sfm_b200 import pnp_ransac
     random.seed(777)
-    pnp_ransac.pnp_ransac_batch(Xs[:8], xs[:8], scenes.K_REF)                 # warm
+    pnp_ransac.pnp_ransac_batch(Xs, xs, scenes.K_REF)                         # warm at full size (allocator, pinned pages)
     torch.cuda.synchronize()
     random.seed(777)
     t0 = time.perf_counter()
