@@ -1314,10 +1314,15 @@ ba_s_pack_sparse_kernel(double *__restrict__ S, size_t ld, int npad, int n, cons
 
 // ------------------------------------------------------------------------------ update (K12)
 // partial sums layout (4 doubles): [s.g, |D s|^2, |D x_new|^2, |D x_cur|^2]
-__global__ void __launch_bounds__(256)
-ba_update_cams_kernel(const double *__restrict__ cam, const double *__restrict__ dc, const double *__restrict__ gc,
-                      const double *__restrict__ Dc, int n, int contribute, double *__restrict__ cam_new,
-                      double *__restrict__ part) {
+struct UpdateCamsArgs {
+    const double *cam, *dc, *gc, *Dc;
+    int n, contribute;
+    double *cam_new, *part;
+};
+
+__device__ __forceinline__ void update_cams_body(const double *__restrict__ cam, const double *__restrict__ dc,
+                                                 const double *__restrict__ gc, const double *__restrict__ Dc, int n,
+                                                 int contribute, double *__restrict__ cam_new, double *__restrict__ part) {
     __shared__ double sred[32];
     double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
     for (int j = threadIdx.x; j < n; j += 256) {
@@ -1336,11 +1341,17 @@ ba_update_cams_kernel(const double *__restrict__ cam, const double *__restrict__
     }
 }
 
-// tp[p] = sum over the observations of p of W_o^T dc[cam(o)]   (thread per observation)
+// tp[p] = sum over the observations of p of W_o^T dc[cam(o)]   (thread per observation). The camera update
+// (x_new = x - dc and its four partial sums; one block of work, independent of this kernel's) rides along as
+// the LAST block of the grid instead of a launch of its own.
 __global__ void __launch_bounds__(256)
 ba_point_rhs_kernel(const double *__restrict__ W, int nobs, const int32_t *__restrict__ cam_idx,
                     const int32_t *__restrict__ pt_idx, const int32_t *__restrict__ pt_ptr,
-                    const double *__restrict__ dc, double *__restrict__ tp) {
+                    const double *__restrict__ dc, double *__restrict__ tp, UpdateCamsArgs uc) {
+    if (blockIdx.x == gridDim.x - 1) {
+        update_cams_body(uc.cam, uc.dc, uc.gc, uc.Dc, uc.n, uc.contribute, uc.cam_new, uc.part);
+        return;
+    }
     const int lane = threadIdx.x & 31;
     const int o = blockIdx.x * 256 + threadIdx.x;
     int p = -1;
@@ -2378,9 +2389,8 @@ static int ba_solve_impl(double *d_cam, double *d_pts, const double *d_obs, cons
                     hp[1] * 1e-3, hp[2] * 1e-3, hp[3] * 1e-3, hp[4] * 1e-3, hp[5] * 1e-3);
         }
         const int nxt = cur ^ 1;
-        ba_update_cams_kernel<<<1, 256, 0, st>>>(pl.cam[cur], pl.dc, pl.gc, pl.Dc, n, rank == 0, pl.cam[nxt], pl.updpart);
-        SFM_LAUNCH_CHECK();
-        ba_point_rhs_kernel<<<ceil_div(nobs, 256), 256, 0, st>>>(pl.W, nobs, d_cam_idx, d_pt_idx, pl.pt_ptr, pl.dc, pl.tp);
+        const UpdateCamsArgs uc{pl.cam[cur], pl.dc, pl.gc, pl.Dc, n, rank == 0, pl.cam[nxt], pl.updpart};
+        ba_point_rhs_kernel<<<ceil_div(nobs, 256) + 1, 256, 0, st>>>(pl.W, nobs, d_cam_idx, d_pt_idx, pl.pt_ptr, pl.dc, pl.tp, uc);
         SFM_LAUNCH_CHECK();
         ba_update_points_kernel<<<pl.grid_pts, 256, 0, st>>>(pl.pts[cur], pl.Vinv, pl.bp, pl.tp, pl.gp, pl.Dp, np,
                                                              pl.pts[nxt], pl.updpart);
